@@ -1,0 +1,719 @@
+// defl_b200.cu -- C-ABI of the B200 inflate engine (libdefl_b200.so).
+//
+// Host side of the drop-in boundary: the reference's public functions
+// (/root/reference/include/defl/infl.h:31-189, implemented there by src/infl/infl.c:1507-1695,
+// src/infl/mem.c:114-361 and src/infl/stream.c:468-794) re-implemented as a thin layer that
+// describes the work to the sm_100a kernels in kernels.cuh.  There is deliberately no CPU
+// decode path in this file: without a usable CUDA device every call fails.
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <atomic>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <memory>
+#include <mutex>
+#include <numeric>
+#include <string>
+#include <thread>
+#include <vector>
+
+#include "../../include/defl/infl.h"
+#include "../../include/defl/infl_batch.h"
+#include "../../include/defl/version.h"
+#include "kernels.cuh"
+
+namespace {
+
+using defl::GroupSmem;
+
+thread_local std::string      g_last_error;
+std::atomic<uint64_t>         g_launches{0};
+std::atomic<int>              g_lanes_per_stream{0};
+
+constexpr int kDefaultLanes = 8;
+
+int fail(const char* what, cudaError_t e = cudaSuccess) {
+  g_last_error = what;
+  if (e != cudaSuccess) {
+    g_last_error += ": ";
+    g_last_error += cudaGetErrorString(e);
+  }
+  return UNZ_ERR;
+}
+
+#define CU_TRY(expr, what)                        \
+  do {                                            \
+    cudaError_t _e = (expr);                      \
+    if (_e != cudaSuccess) return fail(what, _e); \
+  } while (0)
+
+// ---- per-device engine state: cached staging buffers, one worker stream ------------------------
+struct DevBuf {
+  void*  p   = nullptr;
+  size_t cap = 0;
+  int reserve(size_t n) {
+    if (n <= cap) return UNZ_OK;
+    if (p) cudaFree(p);
+    p = nullptr; cap = 0;
+    size_t want = std::max<size_t>(n + n / 4, 1 << 20);
+    cudaError_t e = cudaMalloc(&p, want);
+    if (e != cudaSuccess) { e = cudaMalloc(&p, n); want = n; }
+    if (e != cudaSuccess) return fail("cudaMalloc (staging)", e);
+    cap = want;
+    return UNZ_OK;
+  }
+};
+
+struct PinBuf {
+  void*  p   = nullptr;
+  size_t cap = 0;
+  int reserve(size_t n) {
+    if (n <= cap) return UNZ_OK;
+    if (p) cudaFreeHost(p);
+    p = nullptr; cap = 0;
+    size_t want = std::max<size_t>(n + n / 4, 1 << 16);
+    cudaError_t e = cudaMallocHost(&p, want);
+    if (e != cudaSuccess) return fail("cudaMallocHost", e);
+    cap = want;
+    return UNZ_OK;
+  }
+};
+
+struct Engine {
+  int          dev      = -1;
+  int          sms      = 0;
+  cudaStream_t stream   = nullptr;
+  std::mutex   mu;
+  DevBuf       d_in, d_out, d_items, d_results, d_order, d_ws, d_seg;
+  PinBuf       h_items, h_results, h_order, h_pack, h_seg;
+  bool         ready = false;
+};
+
+constexpr int kMaxDevices = 16;
+Engine        g_engines[kMaxDevices];
+std::mutex    g_engine_mu;
+
+int engine_for_current_device(Engine** out) {
+  int dev = 0;
+  CU_TRY(cudaGetDevice(&dev), "cudaGetDevice (is a CUDA device visible? this library has no CPU path)");
+  if (dev < 0 || dev >= kMaxDevices) return fail("device index out of range");
+  Engine& e = g_engines[dev];
+  if (!e.ready) {
+    std::lock_guard<std::mutex> g(g_engine_mu);
+    if (!e.ready) {
+      cudaDeviceProp prop;
+      CU_TRY(cudaGetDeviceProperties(&prop, dev), "cudaGetDeviceProperties");
+      if (prop.major < 10) return fail("this build contains sm_100a code only (needs a B200-class GPU)");
+      e.dev = dev;
+      e.sms = prop.multiProcessorCount;
+      CU_TRY(cudaStreamCreateWithFlags(&e.stream, cudaStreamNonBlocking), "cudaStreamCreate");
+      e.ready = true;
+    }
+  }
+  *out = &e;
+  return UNZ_OK;
+}
+
+// ---- kernel launch ------------------------------------------------------------------------------------
+template <int G, int GROUPS>
+int launch_batch(int sms, const infl_batch_item_t* d_items, const uint32_t* d_order, uint32_t n, int flags,
+                 infl_batch_result_t* d_results, unsigned int* d_ticket, cudaStream_t st) {
+  auto         kern = defl::inflate_batch_kernel<G, GROUPS>;
+  const size_t smem = sizeof(GroupSmem) * GROUPS;
+  static int   ctas_per_sm[kMaxDevices] = {0};
+  int          dev = 0;
+  cudaGetDevice(&dev);
+  if (!ctas_per_sm[dev]) {
+    CU_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem),
+           "cudaFuncSetAttribute(smem)");
+    int occ = 0;
+    CU_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, G * GROUPS, smem), "occupancy query");
+    if (occ < 1) return fail("inflate kernel does not fit on an SM");
+    ctas_per_sm[dev] = occ;
+  }
+  // persistent grid: a whole number of CTAs per SM, never more groups than streams
+  uint64_t grid = (uint64_t)sms * ctas_per_sm[dev];
+  grid = std::min<uint64_t>(grid, (n + GROUPS - 1) / GROUPS);
+  grid = std::max<uint64_t>(grid, 1);
+  CU_TRY(cudaMemsetAsync(d_ticket, 0, sizeof(unsigned int), st), "cudaMemsetAsync(ticket)");
+  kern<<<(unsigned)grid, G * GROUPS, smem, st>>>(d_items, d_order, n, flags, d_results, d_ticket);
+  CU_TRY(cudaGetLastError(), "inflate_batch_kernel launch");
+  g_launches.fetch_add(1, std::memory_order_relaxed);
+  return UNZ_OK;
+}
+
+int launch_batch_any(int sms, const infl_batch_item_t* d_items, const uint32_t* d_order, size_t n, int flags,
+                     infl_batch_result_t* d_results, void* d_ws, cudaStream_t st) {
+  if (n == 0) return UNZ_OK;
+  if (n > 0xFFFFFFFFull) return fail("batch too large (n must fit 32 bits)");
+  int  lanes = g_lanes_per_stream.load();
+  if (!lanes) lanes = kDefaultLanes;
+  auto t = static_cast<unsigned int*>(d_ws);
+  switch (lanes) {
+    case 1:  return launch_batch<1, 32>(sms, d_items, d_order, (uint32_t)n, flags, d_results, t, st);
+    case 2:  return launch_batch<2, 16>(sms, d_items, d_order, (uint32_t)n, flags, d_results, t, st);
+    case 4:  return launch_batch<4, 16>(sms, d_items, d_order, (uint32_t)n, flags, d_results, t, st);
+    case 8:  return launch_batch<8, 16>(sms, d_items, d_order, (uint32_t)n, flags, d_results, t, st);
+    case 16: return launch_batch<16, 8>(sms, d_items, d_order, (uint32_t)n, flags, d_results, t, st);
+    case 32: return launch_batch<32, 4>(sms, d_items, d_order, (uint32_t)n, flags, d_results, t, st);
+    default: return fail("lanes per stream must be 1, 2, 4, 8, 16 or 32");
+  }
+}
+
+// largest compressed stream first: the longest serial decode starts earliest
+void size_order(const infl_batch_item_t* items, size_t n, uint32_t* order) {
+  std::iota(order, order + n, 0u);
+  std::stable_sort(order, order + n,
+                   [&](uint32_t a, uint32_t b) { return items[a].srclen > items[b].srclen; });
+}
+
+constexpr size_t kAlign = 16;
+inline size_t align_up(size_t v) { return (v + kAlign - 1) & ~(kAlign - 1); }
+
+// ---- host-pointer batch on ONE device: stage in, decode, stage out ----------------------------------------
+// Inputs that are adjacent in host memory travel as one copy; so do outputs.
+int run_host_batch_on_device(const infl_batch_item_t* items, size_t n, int flags,
+                             infl_batch_result_t* results) {
+  Engine* E = nullptr;
+  if (engine_for_current_device(&E) != UNZ_OK) return UNZ_ERR;
+  std::lock_guard<std::mutex> guard(E->mu);
+  cudaStream_t st = E->stream;
+
+  struct Run { const uint8_t* h; size_t len; size_t dev_off; size_t first; size_t count; };
+  std::vector<Run>    in_runs, out_runs;
+  std::vector<size_t> in_off(n), out_off(n);
+  size_t in_total = 0, out_total = 0;
+
+  for (size_t i = 0; i < n; i++) {
+    const uint8_t* s = static_cast<const uint8_t*>(items[i].src);
+    if (items[i].srclen > 0xFFFFFFFFull || items[i].dstlen > 0xFFFFFFFFull)
+      return fail("stream larger than 4 GiB - 1 (the reference API limit)");
+    if (!in_runs.empty() && s == in_runs.back().h + in_runs.back().len) {
+      in_off[i] = in_runs.back().dev_off + in_runs.back().len;
+      in_runs.back().len += items[i].srclen;
+      in_runs.back().count++;
+    } else {
+      // keep the device copy congruent to the host pointer mod 16 (same alignment behaviour)
+      in_total = align_up(in_total) + ((uintptr_t)s & (kAlign - 1));
+      in_runs.push_back({s, (size_t)items[i].srclen, in_total, i, 1});
+      in_off[i] = in_total;
+    }
+    in_total = in_runs.back().dev_off + in_runs.back().len;
+
+    const uint8_t* d = static_cast<const uint8_t*>(items[i].dst);
+    if (!out_runs.empty() && d == out_runs.back().h + out_runs.back().len) {
+      out_off[i] = out_runs.back().dev_off + out_runs.back().len;
+      out_runs.back().len += items[i].dstlen;
+      out_runs.back().count++;
+    } else {
+      out_total = align_up(out_total) + ((uintptr_t)d & (kAlign - 1));
+      out_runs.push_back({d, (size_t)items[i].dstlen, out_total, i, 1});
+      out_off[i] = out_total;
+    }
+    out_total = out_runs.back().dev_off + out_runs.back().len;
+  }
+
+  if (E->d_in.reserve(in_total + 64) || E->d_out.reserve(out_total + 64) ||
+      E->d_items.reserve(n * sizeof(infl_batch_item_t)) || E->d_results.reserve(n * sizeof(infl_batch_result_t)) ||
+      E->d_order.reserve(n * sizeof(uint32_t)) || E->d_ws.reserve(256) ||
+      E->h_items.reserve(n * sizeof(infl_batch_item_t)) || E->h_results.reserve(n * sizeof(infl_batch_result_t)) ||
+      E->h_order.reserve(n * sizeof(uint32_t)))
+    return UNZ_ERR;
+
+  auto* hi = static_cast<infl_batch_item_t*>(E->h_items.p);
+  auto* ho = static_cast<uint32_t*>(E->h_order.p);
+  auto* hr = static_cast<infl_batch_result_t*>(E->h_results.p);
+  uint8_t* din  = static_cast<uint8_t*>(E->d_in.p);
+  uint8_t* dout = static_cast<uint8_t*>(E->d_out.p);
+  for (size_t i = 0; i < n; i++) {
+    hi[i].src = din + in_off[i];   hi[i].srclen = items[i].srclen;
+    hi[i].dst = dout + out_off[i]; hi[i].dstlen = items[i].dstlen;
+  }
+  size_order(items, n, ho);
+
+  for (const Run& r : in_runs)
+    if (r.len) CU_TRY(cudaMemcpyAsync(din + r.dev_off, r.h, r.len, cudaMemcpyHostToDevice, st), "H2D input");
+  CU_TRY(cudaMemcpyAsync(E->d_items.p, hi, n * sizeof(*hi), cudaMemcpyHostToDevice, st), "H2D descriptors");
+  CU_TRY(cudaMemcpyAsync(E->d_order.p, ho, n * sizeof(*ho), cudaMemcpyHostToDevice, st), "H2D order");
+
+  if (launch_batch_any(E->sms, static_cast<infl_batch_item_t*>(E->d_items.p), static_cast<uint32_t*>(E->d_order.p),
+                       n, flags, static_cast<infl_batch_result_t*>(E->d_results.p), E->d_ws.p, st) != UNZ_OK)
+    return UNZ_ERR;
+
+  CU_TRY(cudaMemcpyAsync(hr, E->d_results.p, n * sizeof(*hr), cudaMemcpyDeviceToHost, st), "D2H results");
+  CU_TRY(cudaStreamSynchronize(st), "inflate kernel");
+
+  // outputs: a whole run in one copy when every stream filled its buffer exactly,
+  // otherwise only the bytes each stream produced
+  for (const Run& r : out_runs) {
+    bool exact = r.len != 0;
+    for (size_t k = r.first; exact && k < r.first + r.count; k++)
+      exact = hr[k].code == UNZ_OK && hr[k].outlen == items[k].dstlen;
+    if (exact) {
+      CU_TRY(cudaMemcpyAsync(const_cast<uint8_t*>(r.h), dout + r.dev_off, r.len, cudaMemcpyDeviceToHost, st),
+             "D2H output");
+    } else {
+      for (size_t k = r.first; k < r.first + r.count; k++)
+        if (hr[k].outlen)
+          CU_TRY(cudaMemcpyAsync(items[k].dst, dout + out_off[k], hr[k].outlen, cudaMemcpyDeviceToHost, st),
+                 "D2H output");
+    }
+  }
+  CU_TRY(cudaStreamSynchronize(st), "D2H output");
+  std::memcpy(results, hr, n * sizeof(*hr));
+  return UNZ_OK;
+}
+
+// ---- device-pointer batch: only descriptors and results cross the bus ---------------------------------------
+int run_device_batch(const infl_batch_item_t* items, size_t n, int flags, infl_batch_result_t* results) {
+  Engine* E = nullptr;
+  if (engine_for_current_device(&E) != UNZ_OK) return UNZ_ERR;
+  std::lock_guard<std::mutex> guard(E->mu);
+  cudaStream_t st = E->stream;
+  if (E->d_items.reserve(n * sizeof(infl_batch_item_t)) || E->d_results.reserve(n * sizeof(infl_batch_result_t)) ||
+      E->d_order.reserve(n * sizeof(uint32_t)) || E->d_ws.reserve(256) ||
+      E->h_order.reserve(n * sizeof(uint32_t)))
+    return UNZ_ERR;
+  auto* ho = static_cast<uint32_t*>(E->h_order.p);
+  size_order(items, n, ho);
+  CU_TRY(cudaMemcpyAsync(E->d_items.p, items, n * sizeof(*items), cudaMemcpyHostToDevice, st), "H2D descriptors");
+  CU_TRY(cudaMemcpyAsync(E->d_order.p, ho, n * sizeof(*ho), cudaMemcpyHostToDevice, st), "H2D order");
+  if (launch_batch_any(E->sms, static_cast<infl_batch_item_t*>(E->d_items.p), static_cast<uint32_t*>(E->d_order.p),
+                       n, flags, static_cast<infl_batch_result_t*>(E->d_results.p), E->d_ws.p, st) != UNZ_OK)
+    return UNZ_ERR;
+  CU_TRY(cudaMemcpyAsync(results, E->d_results.p, n * sizeof(*results), cudaMemcpyDeviceToHost, st), "D2H results");
+  CU_TRY(cudaStreamSynchronize(st), "inflate kernel");
+  return UNZ_OK;
+}
+
+// ---- multi-GPU sharding of a host batch: byte-balanced, no collective ----------------------------
+// Greedy longest-processing-time assignment on B_alg = compressed + decompressed bytes.
+void partition_lpt(const infl_batch_item_t* items, size_t n, int ngpu, std::vector<std::vector<uint32_t>>& parts) {
+  std::vector<uint32_t> idx(n);
+  std::iota(idx.begin(), idx.end(), 0u);
+  auto weight = [&](uint32_t i) { return items[i].srclen + items[i].dstlen; };
+  std::stable_sort(idx.begin(), idx.end(), [&](uint32_t a, uint32_t b) { return weight(a) > weight(b); });
+  std::vector<uint64_t> load(ngpu, 0);
+  parts.assign(ngpu, {});
+  for (uint32_t i : idx) {
+    int g = (int)(std::min_element(load.begin(), load.end()) - load.begin());
+    parts[g].push_back(i);
+    load[g] += weight(i) + 1;
+  }
+  for (auto& p : parts) std::sort(p.begin(), p.end());  // keep host adjacency => few large copies
+}
+
+int run_host_batch_all_gpus(const infl_batch_item_t* items, size_t n, int flags, infl_batch_result_t* results) {
+  int ngpu = 0;
+  CU_TRY(cudaGetDeviceCount(&ngpu), "cudaGetDeviceCount");
+  if (ngpu <= 1 || n < 2) return run_host_batch_on_device(items, n, flags, results);
+  ngpu = std::min(ngpu, kMaxDevices);
+  std::vector<std::vector<uint32_t>> parts;
+  partition_lpt(items, n, ngpu, parts);
+  std::vector<int>         rc(ngpu, UNZ_OK);
+  std::vector<std::string> err(ngpu);
+  std::vector<std::thread> th;
+  for (int g = 0; g < ngpu; g++) {
+    th.emplace_back([&, g]() {
+      if (parts[g].empty()) return;
+      if (cudaSetDevice(g) != cudaSuccess) { rc[g] = UNZ_ERR; err[g] = "cudaSetDevice"; return; }
+      std::vector<infl_batch_item_t>   sub(parts[g].size());
+      std::vector<infl_batch_result_t> res(parts[g].size());
+      for (size_t k = 0; k < sub.size(); k++) sub[k] = items[parts[g][k]];
+      rc[g] = run_host_batch_on_device(sub.data(), sub.size(), flags, res.data());
+      if (rc[g] != UNZ_OK) { err[g] = g_last_error; return; }
+      for (size_t k = 0; k < sub.size(); k++) results[parts[g][k]] = res[k];
+    });
+  }
+  for (auto& t : th) t.join();
+  for (int g = 0; g < ngpu; g++)
+    if (rc[g] != UNZ_OK) return fail(err[g].c_str());
+  return UNZ_OK;
+}
+
+}  // namespace
+
+// =====================================================================================================
+//                                         exported C ABI
+// =====================================================================================================
+extern "C" {
+
+UNZ_EXPORT int infl_device_count(void) {
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess) return 0;
+  return n;
+}
+
+UNZ_EXPORT const char* infl_last_error(void) { return g_last_error.c_str(); }
+
+UNZ_EXPORT const char* infl_engine_info(void) {
+  static char buf[256];
+  int lanes = g_lanes_per_stream.load();
+  std::snprintf(buf, sizeof(buf),
+                "defl_b200 %d.%d sm_100a; lanes/stream=%d; smem/stream=%zu B; lit root %d bits, dist root %d bits",
+                DEFL_B200_VERSION_MAJOR, DEFL_B200_VERSION_MINOR, lanes ? lanes : kDefaultLanes,
+                sizeof(GroupSmem), defl::kLitRootBits, defl::kDistRootBits);
+  return buf;
+}
+
+UNZ_EXPORT uint64_t infl_kernel_launch_count(void) { return g_launches.load(); }
+
+UNZ_EXPORT int infl_set_lanes_per_stream(int lanes) {
+  if (lanes != 0 && lanes != 1 && lanes != 2 && lanes != 4 && lanes != 8 && lanes != 16 && lanes != 32)
+    return fail("lanes per stream must be 0 (default), 1, 2, 4, 8, 16 or 32");
+  g_lanes_per_stream.store(lanes);
+  return UNZ_OK;
+}
+
+UNZ_EXPORT size_t infl_batch_workspace_size(size_t n) {
+  (void)n;
+  return 256;
+}
+
+UNZ_EXPORT int infl_batch_decode_device(const infl_batch_item_t* d_items, const uint32_t* d_order, size_t n,
+                                        int flags, infl_batch_result_t* d_results, void* d_workspace,
+                                        void* cuda_stream) {
+  if (n == 0) return UNZ_OK;
+  if (!d_items || !d_results || !d_workspace) return fail("null device pointer");
+  Engine* E = nullptr;
+  if (engine_for_current_device(&E) != UNZ_OK) return UNZ_ERR;
+  return launch_batch_any(E->sms, d_items, d_order, n, flags, d_results, d_workspace,
+                          static_cast<cudaStream_t>(cuda_stream));
+}
+
+UNZ_EXPORT int infl_gather_device(const void* const* d_seg_src, const uint64_t* d_seg_len,
+                                  const uint64_t* d_seg_dst_off, size_t nseg, void* d_out, void* cuda_stream) {
+  if (nseg == 0) return UNZ_OK;
+  Engine* E = nullptr;
+  if (engine_for_current_device(&E) != UNZ_OK) return UNZ_ERR;
+  const uint64_t warps  = std::min<uint64_t>(nseg, (uint64_t)E->sms * 64);
+  const unsigned blocks = (unsigned)((warps * 32 + 255) / 256);
+  defl::gather_pieces_kernel<<<blocks, 256, 0, static_cast<cudaStream_t>(cuda_stream)>>>(
+      d_seg_src, d_seg_len, d_seg_dst_off, nseg, static_cast<uint8_t*>(d_out));
+  CU_TRY(cudaGetLastError(), "gather_pieces_kernel launch");
+  g_launches.fetch_add(1, std::memory_order_relaxed);
+  return UNZ_OK;
+}
+
+UNZ_EXPORT int infl_buf_batch(const infl_batch_item_t* items, size_t n, int flags, infl_batch_result_t* results) {
+  if (n == 0) return UNZ_OK;
+  if (!items || !results) return fail("null argument");
+  if (flags & INFL_BATCH_DEVICE_PTRS) return run_device_batch(items, n, flags, results);
+  if (flags & INFL_BATCH_ALL_GPUS) return run_host_batch_all_gpus(items, n, flags, results);
+  return run_host_batch_on_device(items, n, flags, results);
+}
+
+// Chunk-list batch.  Pieces are never joined by the host CPU:
+//  * device pieces: a (src, len, dst offset) descriptor table drives gather_pieces_kernel;
+//  * host pieces >= 8 KiB: one DMA each, landing at their logical offset in HBM;
+//  * host pieces < 8 KiB are packed into a pinned bounce buffer on their way to the copy
+//    engine (the reference packs exactly these itself, mem.c:121-155, threshold common.h:46).
+UNZ_EXPORT int infl_buf_batch_iov(const infl_batch_iov_item_t* items, size_t n, int flags,
+                                  infl_batch_result_t* results) {
+  if (n == 0) return UNZ_OK;
+  if (!items || !results) return fail("null argument");
+  Engine* E = nullptr;
+  if (engine_for_current_device(&E) != UNZ_OK) return UNZ_ERR;
+
+  const bool dev_ptrs = (flags & INFL_BATCH_DEVICE_PTRS) != 0;
+  std::vector<size_t> in_off(n + 1, 0), out_off(n + 1, 0);
+  size_t nseg = 0;
+  for (size_t i = 0; i < n; i++) {
+    size_t tot = 0;
+    for (uint64_t k = 0; k < items[i].niov; k++) tot += items[i].iov[k].len;
+    if (tot > 0xFFFFFFFFull || items[i].dstlen > 0xFFFFFFFFull)
+      return fail("stream larger than 4 GiB - 1 (the reference API limit)");
+    in_off[i + 1]  = align_up(in_off[i] + tot);
+    out_off[i + 1] = dev_ptrs ? 0 : align_up(out_off[i] + items[i].dstlen);
+    nseg += items[i].niov;
+  }
+
+  std::vector<infl_batch_item_t>   flat(n);
+  std::vector<infl_batch_result_t> res(n);
+  std::vector<uint32_t>            live;   // streams that actually have pieces
+  int rc = UNZ_OK;
+  {
+    std::lock_guard<std::mutex> guard(E->mu);
+    cudaStream_t st = E->stream;
+    if (E->d_in.reserve(in_off[n] + 64) || (!dev_ptrs && E->d_out.reserve(out_off[n] + 64))) return UNZ_ERR;
+    uint8_t* din  = static_cast<uint8_t*>(E->d_in.p);
+    uint8_t* dout = static_cast<uint8_t*>(E->d_out.p);
+
+    if (dev_ptrs) {
+      // descriptor table -> K2
+      if (E->h_seg.reserve(nseg * 24 + 64) || E->d_seg.reserve(nseg * 24 + 64)) return UNZ_ERR;
+      auto* hs_src = static_cast<const void**>(E->h_seg.p);
+      auto* hs_len = reinterpret_cast<uint64_t*>(hs_src + nseg);
+      auto* hs_off = hs_len + nseg;
+      size_t s = 0;
+      for (size_t i = 0; i < n; i++) {
+        size_t at = in_off[i];
+        for (uint64_t k = 0; k < items[i].niov; k++, s++) {
+          hs_src[s] = items[i].iov[k].ptr; hs_len[s] = items[i].iov[k].len; hs_off[s] = at;
+          at += items[i].iov[k].len;
+        }
+      }
+      if (nseg) {
+        CU_TRY(cudaMemcpyAsync(E->d_seg.p, E->h_seg.p, nseg * 24, cudaMemcpyHostToDevice, st), "H2D gather table");
+        auto* ds_src = static_cast<const void* const*>(E->d_seg.p);
+        auto* ds_len = reinterpret_cast<const uint64_t*>(ds_src + nseg);
+        if (infl_gather_device(ds_src, ds_len, ds_len + nseg, nseg, din, st) != UNZ_OK) return UNZ_ERR;
+      }
+    } else {
+      // DMA join; small pieces ride a pinned bounce buffer
+      constexpr size_t kSmall = 8192;
+      size_t small_total = 0;
+      for (size_t i = 0; i < n; i++)
+        for (uint64_t k = 0; k < items[i].niov; k++)
+          if (items[i].iov[k].len < kSmall) small_total += items[i].iov[k].len;
+      if (E->h_pack.reserve(small_total + 64)) return UNZ_ERR;
+      uint8_t* pack = static_cast<uint8_t*>(E->h_pack.p);
+      size_t   pk = 0;
+      for (size_t i = 0; i < n; i++) {
+        size_t at = in_off[i], run_at = 0, run_pk = 0, run_len = 0;
+        auto flush = [&]() -> int {
+          if (run_len)
+            CU_TRY(cudaMemcpyAsync(din + run_at, pack + run_pk, run_len, cudaMemcpyHostToDevice, st), "H2D packed pieces");
+          run_len = 0;
+          return UNZ_OK;
+        };
+        for (uint64_t k = 0; k < items[i].niov; k++) {
+          const size_t len = items[i].iov[k].len;
+          if (len < kSmall) {
+            if (!run_len) { run_at = at; run_pk = pk; }
+            std::memcpy(pack + pk, items[i].iov[k].ptr, len);
+            pk += len; run_len += len;
+          } else {
+            if (flush() != UNZ_OK) return UNZ_ERR;
+            CU_TRY(cudaMemcpyAsync(din + at, items[i].iov[k].ptr, len, cudaMemcpyHostToDevice, st), "H2D piece");
+          }
+          at += len;
+        }
+        if (flush() != UNZ_OK) return UNZ_ERR;
+      }
+    }
+
+    for (size_t i = 0; i < n; i++) {
+      size_t tot = 0;
+      for (uint64_t k = 0; k < items[i].niov; k++) tot += items[i].iov[k].len;
+      flat[i].src = din + in_off[i];
+      flat[i].srclen = tot;
+      flat[i].dst = dev_ptrs ? items[i].dst : static_cast<void*>(dout + out_off[i]);
+      flat[i].dstlen = items[i].dstlen;
+    }
+    if (E->d_items.reserve(n * sizeof(infl_batch_item_t)) || E->d_results.reserve(n * sizeof(infl_batch_result_t)) ||
+        E->d_order.reserve(n * sizeof(uint32_t)) || E->d_ws.reserve(256) || E->h_order.reserve(n * sizeof(uint32_t)))
+      return UNZ_ERR;
+    auto* ho = static_cast<uint32_t*>(E->h_order.p);
+    size_order(flat.data(), n, ho);
+    CU_TRY(cudaMemcpyAsync(E->d_items.p, flat.data(), n * sizeof(flat[0]), cudaMemcpyHostToDevice, st), "H2D descriptors");
+    CU_TRY(cudaMemcpyAsync(E->d_order.p, ho, n * sizeof(*ho), cudaMemcpyHostToDevice, st), "H2D order");
+    rc = launch_batch_any(E->sms, static_cast<infl_batch_item_t*>(E->d_items.p), static_cast<uint32_t*>(E->d_order.p),
+                          n, flags, static_cast<infl_batch_result_t*>(E->d_results.p), E->d_ws.p, st);
+    if (rc != UNZ_OK) return rc;
+    CU_TRY(cudaMemcpyAsync(res.data(), E->d_results.p, n * sizeof(res[0]), cudaMemcpyDeviceToHost, st), "D2H results");
+    CU_TRY(cudaStreamSynchronize(st), "inflate kernel");
+    if (!dev_ptrs) {
+      for (size_t i = 0; i < n; i++)
+        if (res[i].outlen)
+          CU_TRY(cudaMemcpyAsync(items[i].dst, dout + out_off[i], res[i].outlen, cudaMemcpyDeviceToHost, st), "D2H output");
+      CU_TRY(cudaStreamSynchronize(st), "D2H output");
+    }
+  }
+  for (size_t i = 0; i < n; i++) {
+    results[i] = res[i];
+    if (items[i].niov == 0) {   // nothing was ever included: UNZ_NOOP (infl.c:1544-1545,1671-1672)
+      std::memset(&results[i], 0, sizeof(results[i]));
+      results[i].code = UNZ_NOOP;
+      results[i].adler = 1;
+    }
+  }
+  return UNZ_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------
+// The reference's handle API.  The handle is opaque to callers (reference include/defl/common.h:94-96),
+// so its layout is ours: destination, flags and the list of included pieces.
+// ---------------------------------------------------------------------------------------------------
+}  // extern "C"
+
+struct unz__stream_t {
+  uint8_t* dst    = nullptr;
+  uint32_t dstlen = 0;
+  int      flags  = 0;
+  uint32_t dstpos = 0;      // infl_output_pos
+  uint32_t inpos  = 0;      // infl_input_pos
+  uint32_t adler = 1, adler_stored = 0;
+  bool     has_trailer = false;
+  bool     done = false;    // infl_stream(): final block decoded
+
+  // pieces in call order.  Small ones (<= 8 KiB, reference threshold src/common.h:46) are copied
+  // into pages owned by the handle, because the reference lets callers release them right after
+  // infl_include (mem.c:135-151); larger ones are borrowed (README.md:47).
+  std::vector<infl_iovec_t>               pieces;
+  std::vector<std::unique_ptr<uint8_t[]>> pages;
+  size_t page_used = 0, page_cap = 0;
+  bool   last_is_page_tail = false;
+  uint64_t total_in = 0;
+  bool   any_piece = false;
+
+  // infl_stream() shim state
+  std::vector<uint8_t> acc;       // accumulated compressed input
+  bool                 strm_started = false;
+};
+
+namespace {
+
+constexpr size_t kPiecePage      = 1 << 20;
+constexpr size_t kCopyThreshold  = 8192;
+
+void stream_clear_pieces(unz__stream_t* s) {
+  s->pieces.clear();
+  s->pages.clear();
+  s->page_used = s->page_cap = 0;
+  s->last_is_page_tail = false;
+  s->total_in = 0;
+  s->any_piece = false;
+}
+
+void stream_reset_state(unz__stream_t* s) {
+  s->dstpos = 0; s->inpos = 0; s->adler = 1; s->adler_stored = 0; s->has_trailer = false;
+  s->done = false; s->acc.clear(); s->strm_started = false;
+}
+
+int decode_pieces(unz__stream_t* s, const infl_iovec_t* iov, size_t niov, infl_batch_result_t* r) {
+  infl_batch_iov_item_t it;
+  it.iov = iov; it.niov = niov; it.dst = s->dst; it.dstlen = s->dstlen;
+  return infl_buf_batch_iov(&it, 1, s->flags == INFL_ZLIB ? INFL_ZLIB : 0, r);
+}
+
+}  // namespace
+
+extern "C" {
+
+UNZ_EXPORT infl_stream_t* infl_init(void* dst, uint32_t dstlen, int flags) {
+  // the reference only allocates here (infl.c:1677-1695); so do we -- the device is touched in infl()
+  unz__stream_t* s = new (std::nothrow) unz__stream_t();
+  if (!s) return nullptr;
+  s->dst = static_cast<uint8_t*>(dst);
+  s->dstlen = dstlen;
+  s->flags = flags;
+  return s;
+}
+
+UNZ_EXPORT void infl_reset_pool(infl_stream_t* s) {     // mem.c:220-232
+  if (!s) return;
+  stream_clear_pieces(s);
+}
+
+UNZ_EXPORT void infl_reset(infl_stream_t* s, void* dst, uint32_t dstlen, int flags) {  // mem.c:257-275
+  if (!s) return;
+  stream_clear_pieces(s);
+  stream_reset_state(s);
+  s->dst = static_cast<uint8_t*>(dst);
+  s->dstlen = dstlen;
+  s->flags = flags;
+}
+
+UNZ_EXPORT int infl_resize_output(infl_stream_t* s, void* dst, uint32_t dstlen) {      // mem.c:277-288
+  if (!s || !dst || dstlen < s->dstpos) return UNZ_ERR;
+  s->dst = static_cast<uint8_t*>(dst);
+  s->dstlen = dstlen;
+  return UNZ_OK;
+}
+
+UNZ_EXPORT void infl_include(infl_stream_t* s, const void* ptr, uint32_t len) {        // mem.c:114-216
+  if (!s) return;
+  s->any_piece = true;
+  s->total_in += len;
+  if (len <= kCopyThreshold) {
+    if (s->pages.empty() || len > s->page_cap - s->page_used) {
+      std::unique_ptr<uint8_t[]> pg(new (std::nothrow) uint8_t[kPiecePage]);
+      if (!pg) return;   // allocation failure silently drops the piece, as mem.c:191 does
+      s->pages.push_back(std::move(pg));
+      s->page_used = 0; s->page_cap = kPiecePage;
+      s->last_is_page_tail = false;
+    }
+    uint8_t* at = s->pages.back().get() + s->page_used;
+    if (len) std::memcpy(at, ptr, len);
+    s->page_used += len;
+    if (s->last_is_page_tail) s->pieces.back().len += len;   // extend the run inside the page
+    else { s->pieces.push_back({at, len}); s->last_is_page_tail = true; }
+  } else {
+    s->pieces.push_back({ptr, len});
+    s->last_is_page_tail = false;
+  }
+}
+
+UNZ_EXPORT int infl(infl_stream_t* s) {                                                 // infl.c:1507-1675
+  if (!s) return UNZ_ERR;
+  if (!s->any_piece) return UNZ_NOOP;                      // infl.c:1544-1545
+  if (s->total_in == 0) return UNZ_OK;                     // infl.c:1547-1550
+  infl_batch_result_t r;
+  if (decode_pieces(s, s->pieces.data(), s->pieces.size(), &r) != UNZ_OK) return UNZ_ERR;
+  if (r.code != UNZ_OK) return UNZ_ERR;                    // every failure collapses to UNZ_ERR (infl.c:1673-1674)
+  s->dstpos = (uint32_t)r.outlen;
+  s->inpos  = (uint32_t)r.inpos;
+  s->adler = r.adler; s->adler_stored = r.adler_stored;
+  s->has_trailer = (r.info & INFL_INFO_HAS_TRAILER) != 0;
+  s->done = true;
+  return UNZ_OK;
+}
+
+UNZ_EXPORT void infl_destroy(infl_stream_t* s) { delete s; }                             // mem.c:331-361
+
+UNZ_EXPORT int infl_buf(const void* src, uint32_t srclen, void* dst, uint32_t dstlen, int flags) {  // infl.h:125-145
+  infl_batch_item_t   it;
+  infl_batch_result_t r;
+  if (srclen == 0) return UNZ_OK;                          // one empty piece: infl.c:1547-1550
+  it.src = src; it.srclen = srclen; it.dst = dst; it.dstlen = dstlen;
+  if (infl_buf_batch(&it, 1, flags == INFL_ZLIB ? INFL_ZLIB : 0, &r) != UNZ_OK) return UNZ_ERR;
+  return r.code == UNZ_OK ? UNZ_OK : UNZ_ERR;
+}
+
+UNZ_EXPORT uint32_t infl_output_pos(const infl_stream_t* s) { return s ? s->dstpos : 0u; }  // mem.c:290-294
+UNZ_EXPORT uint32_t infl_input_pos(const infl_stream_t* s) { return s ? s->inpos : 0u; }    // mem.c:296-329
+
+UNZ_EXPORT uint32_t infl_adler32(const infl_stream_t* s, uint32_t* stored, int* present) {
+  if (stored) *stored = s ? s->adler_stored : 0u;
+  if (present) *present = (s && s->has_trailer) ? 1 : 0;
+  return s ? s->adler : 1u;
+}
+
+// Resumable decode (reference src/infl/stream.c:468-794) as a host shim: input is accumulated
+// and the whole prefix is offered to the device decoder; a stream that is not complete yet
+// reports UNZ_UNFINISHED, one whose output does not fit reports UNZ_EFULL, and the call after
+// infl_resize_output() decodes again into the larger buffer.  See INTEGRATION.md.
+UNZ_EXPORT int infl_stream(infl_stream_t* s, const void* src, uint32_t srclen) {
+  if (!s) return UNZ_ERR;
+  if (src && srclen) {
+    const uint8_t* p = static_cast<const uint8_t*>(src);
+    s->acc.insert(s->acc.end(), p, p + srclen);
+    s->strm_started = true;
+  } else if (!s->strm_started) {
+    return UNZ_OK;                                          // stream.c:489-493: nothing yet => UNZ_OK
+  }
+  if (s->done) return UNZ_OK;                               // stream.c:496-499
+  if (s->acc.empty()) return UNZ_NOOP;
+  if (s->flags == INFL_ZLIB && s->acc.size() < 2) return UNZ_UNFINISHED;   // stream.c:576-579
+
+  infl_iovec_t        iov{s->acc.data(), s->acc.size()};
+  infl_batch_result_t r;
+  if (decode_pieces(s, &iov, 1, &r) != UNZ_OK) return UNZ_ERR;
+  const uint32_t reason = (r.info >> INFL_INFO_REASON_SHIFT) & 0xFF;
+  if (r.code == UNZ_OK) {
+    s->dstpos = (uint32_t)r.outlen; s->inpos = (uint32_t)r.inpos;
+    s->adler = r.adler; s->adler_stored = r.adler_stored;
+    s->has_trailer = (r.info & INFL_INFO_HAS_TRAILER) != 0;
+    s->done = true;
+    return UNZ_OK;
+  }
+  s->dstpos = (uint32_t)r.outlen;
+  if (reason == defl::R_TRUNCATED) return UNZ_UNFINISHED;   // stream.c:614-616 and friends
+  if (reason == defl::R_OUTPUT_FULL) return UNZ_EFULL;      // stream.c:625-627, :769-770
+  return UNZ_ERR;
+}
+
+}  // extern "C"

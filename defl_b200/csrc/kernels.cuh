@@ -1,0 +1,100 @@
+// kernels.cuh -- __global__ entry points (sm_100a) around the decode core.
+#pragma once
+#include "simt_cuda.cuh"
+#include "inflate_core.cuh"
+#include "../../include/defl/infl_batch.h"
+
+namespace defl {
+
+// K3: batch inflate.  Persistent CTAs; every group of G lanes pulls the next stream from a
+// global ticket counter (streams are pre-ordered largest-first by the host so the tail is
+// short), decodes it start to finish and writes one 32-byte result record.
+template <int G, int GROUPS>
+__global__ void __launch_bounds__(G * GROUPS)
+inflate_batch_kernel(const infl_batch_item_t* __restrict__ items, const uint32_t* __restrict__ order,
+                     uint32_t n, int flags, infl_batch_result_t* __restrict__ results,
+                     unsigned int* __restrict__ ticket) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  GroupSmem& sm = reinterpret_cast<GroupSmem*>(smem_raw)[threadIdx.x / G];
+
+  Lane<G> L;
+  L.wlane = threadIdx.x & 31;
+  L.lane  = threadIdx.x % G;
+  L.gmask = (G == 32) ? 0xFFFFFFFFu : (((1u << G) - 1u) << (L.wlane & ~(G - 1)));
+
+  for (;;) {
+    uint32_t k = 0;
+    if (L.lane == 0) k = atomicAdd(ticket, 1u);
+    if (G > 1) k = simt::shfl(L.gmask, k, L.wlane & ~(G - 1));
+    if (k >= n) break;
+    const uint32_t idx = order ? order[k] : k;
+    const infl_batch_item_t it = items[idx];
+
+    StreamOut o;
+    if (it.srclen > 0xFFFFFFFFull || it.dstlen > 0xFFFFFFFFull) {
+      o.code = -1; o.adler = 1; o.outlen = 0; o.inpos = 0; o.adler_stored = 0; o.info = R_TRUNCATED << 8;
+    } else {
+      inflate_stream<G>(L, sm, static_cast<const uint8_t*>(it.src), (uint32_t)it.srclen,
+                        static_cast<uint8_t*>(it.dst), (uint32_t)it.dstlen, flags, o);
+    }
+    if (L.lane == 0) {
+      infl_batch_result_t r;
+      r.code = o.code; r.adler = o.adler; r.outlen = o.outlen; r.inpos = o.inpos;
+      r.adler_stored = o.adler_stored; r.info = o.info;
+      results[idx] = r;
+    }
+    simt::syncwarp(L.gmask);
+  }
+}
+
+// K2: descriptor-driven gather of input pieces into contiguous device memory (replaces the
+// host-side join of infl_include, reference src/infl/mem.c:121-155, and the chunk walk of
+// REFILL, infl.c:1121-1128).  One warp per piece per trip; 16-byte stores when the
+// destination allows, byte-exact for any alignment and length (including 0 and 1).
+__global__ void __launch_bounds__(256)
+gather_pieces_kernel(const void* const* __restrict__ seg_src, const uint64_t* __restrict__ seg_len,
+                     const uint64_t* __restrict__ seg_dst_off, uint64_t nseg,
+                     uint8_t* __restrict__ out) {
+  const uint32_t lane   = threadIdx.x & 31;
+  const uint64_t warp   = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const uint64_t nwarps = ((uint64_t)gridDim.x * blockDim.x) >> 5;
+  for (uint64_t s = warp; s < nseg; s += nwarps) {
+    const uint8_t* src = static_cast<const uint8_t*>(seg_src[s]);
+    uint8_t*       dst = out + seg_dst_off[s];
+    uint64_t       n   = seg_len[s];
+    uint64_t head = (16u - ((uintptr_t)dst & 15u)) & 15u;
+    if (head > n) head = n;
+    for (uint64_t j = lane; j < head; j += 32) dst[j] = __ldg(src + j);
+    src += head; dst += head; n -= head;
+    const uint64_t nvec = n >> 4;
+    if (((uintptr_t)src & 15u) == 0) {
+      const uint4* s4 = reinterpret_cast<const uint4*>(src);
+      uint4*       d4 = reinterpret_cast<uint4*>(dst);
+      for (uint64_t k = lane; k < nvec; k += 32) d4[k] = __ldg(s4 + k);
+    } else if (((uintptr_t)src & 3u) == 0) {
+      const uint32_t* s1 = reinterpret_cast<const uint32_t*>(src);
+      uint4*          d4 = reinterpret_cast<uint4*>(dst);
+      for (uint64_t k = lane; k < nvec; k += 32) {
+        uint4 v;
+        v.x = __ldg(s1 + 4 * k); v.y = __ldg(s1 + 4 * k + 1);
+        v.z = __ldg(s1 + 4 * k + 2); v.w = __ldg(s1 + 4 * k + 3);
+        d4[k] = v;
+      }
+    } else {
+      const uint32_t  sh = (uint32_t)((uintptr_t)src & 3u) * 8u;
+      const uint32_t* s1 = reinterpret_cast<const uint32_t*>((uintptr_t)src & ~(uintptr_t)3);
+      uint4*          d4 = reinterpret_cast<uint4*>(dst);
+      for (uint64_t k = lane; k < nvec; k += 32) {
+        const uint32_t a = __ldg(s1 + 4 * k), b = __ldg(s1 + 4 * k + 1), c = __ldg(s1 + 4 * k + 2),
+                       d = __ldg(s1 + 4 * k + 3), e = __ldg(s1 + 4 * k + 4);
+        uint4 v;
+        v.x = __funnelshift_r(a, b, sh); v.y = __funnelshift_r(b, c, sh);
+        v.z = __funnelshift_r(c, d, sh); v.w = __funnelshift_r(d, e, sh);
+        d4[k] = v;
+      }
+    }
+    for (uint64_t j = (nvec << 4) + lane; j < n; j += 32) dst[j] = __ldg(src + j);
+  }
+}
+
+}  // namespace defl

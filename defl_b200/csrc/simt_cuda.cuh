@@ -1,0 +1,39 @@
+// simt_cuda.cuh -- the warp-level primitives the inflate core uses, as sm_100a intrinsics.
+// (tests/emu/simt_emu.h provides the same names on the CPU for a lock-step emulator that
+//  exists only to debug the decode logic without a GPU; it is never part of the product.)
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#define DEFL_DEV __device__ __forceinline__
+#define DEFL_DEV_NOINLINE __device__ __noinline__
+
+namespace simt {
+
+DEFL_DEV void     syncwarp(unsigned mask) { __syncwarp(mask); }
+DEFL_DEV uint32_t shfl(unsigned mask, uint32_t v, int src_lane) { return __shfl_sync(mask, v, src_lane); }
+DEFL_DEV unsigned match_any(unsigned mask, uint32_t v) { return __match_any_sync(mask, v); }
+DEFL_DEV unsigned lanemask_lt() {
+  unsigned m;
+  asm("mov.u32 %0, %%lanemask_lt;" : "=r"(m));
+  return m;
+}
+DEFL_DEV uint32_t atomic_add_shared(uint32_t* p, uint32_t v) { return atomicAdd(p, v); }
+DEFL_DEV uint32_t funnel_r(uint32_t lo, uint32_t hi, uint32_t sh) { return __funnelshift_r(lo, hi, sh); }
+DEFL_DEV uint32_t brev(uint32_t v) { return __brev(v); }
+DEFL_DEV int      popc(uint32_t v) { return __popc(v); }
+DEFL_DEV uint32_t bfe(uint32_t v, uint32_t pos, uint32_t len) {
+  uint32_t r;
+  asm("bfe.u32 %0, %1, %2, %3;" : "=r"(r) : "r"(v), "r"(pos), "r"(len));
+  return r;
+}
+DEFL_DEV uint32_t dp4a(uint32_t a, uint32_t b, uint32_t c) { return __dp4a(a, b, c); }
+DEFL_DEV uint32_t byte_perm(uint32_t a, uint32_t b, uint32_t s) { return __byte_perm(a, b, s); }
+
+// compressed input: read-only for the whole kernel -> non-coherent path
+DEFL_DEV uint32_t ld_in32(const uint32_t* p) { return __ldg(p); }
+DEFL_DEV uint8_t  ld_in8(const uint8_t* p) { return __ldg(p); }
+DEFL_DEV uint4    ld_in128(const uint4* p) { return __ldg(p); }
+DEFL_DEV void     prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
+
+}  // namespace simt

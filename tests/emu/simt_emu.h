@@ -1,0 +1,73 @@
+// tests/emu/simt_emu.h -- DEBUG AID, TEST TREE ONLY.
+// Lock-step CPU emulation of the few warp primitives defl_b200/csrc/inflate_core.cuh uses, so the
+// decode *logic* (bit reader, table construction, copies, Adler) can be exercised in the CPU
+// container, where there is no GPU.  G lanes of one group run as G host threads that meet at a
+// barrier wherever the kernel calls __syncwarp / __shfl_sync / __match_any_sync.
+// It is not a decode path of the product: nothing under defl_b200/ or include/ references it,
+// it is built only by tests/test_emu_logic.py, and the GPU tests never load it.
+#pragma once
+#include <pthread.h>
+#include <stdint.h>
+#include <string.h>
+
+#define DEFL_DEV inline
+#define DEFL_DEV_NOINLINE inline
+
+namespace simt {
+
+struct Group {
+  int               G;
+  pthread_barrier_t bar;
+  uint32_t          xchg[32];
+};
+static thread_local Group* t_group = nullptr;
+static thread_local int    t_lane  = 0;
+
+inline void barrier() { if (t_group->G > 1) pthread_barrier_wait(&t_group->bar); }
+
+inline void syncwarp(unsigned) { barrier(); }
+inline uint32_t shfl(unsigned, uint32_t v, int src) {
+  if (t_group->G == 1) return v;
+  t_group->xchg[t_lane] = v;
+  barrier();
+  uint32_t r = t_group->xchg[src];
+  barrier();
+  return r;
+}
+inline unsigned match_any(unsigned, uint32_t v) {
+  if (t_group->G == 1) return 1u;
+  t_group->xchg[t_lane] = v;
+  barrier();
+  unsigned m = 0;
+  for (int i = 0; i < t_group->G; i++)
+    if (t_group->xchg[i] == v) m |= 1u << i;
+  barrier();
+  return m;
+}
+inline unsigned lanemask_lt() { return (1u << t_lane) - 1u; }
+inline uint32_t atomic_add_shared(uint32_t* p, uint32_t v) { return __atomic_fetch_add(p, v, __ATOMIC_RELAXED); }
+inline uint32_t funnel_r(uint32_t lo, uint32_t hi, uint32_t sh) {
+  sh &= 31u;
+  return sh ? (lo >> sh) | (hi << (32u - sh)) : lo;
+}
+inline uint32_t brev(uint32_t v) {
+  uint32_t r = 0;
+  for (int i = 0; i < 32; i++) { r = (r << 1) | (v & 1u); v >>= 1; }
+  return r;
+}
+inline int popc(uint32_t v) { return __builtin_popcount(v); }
+inline uint32_t bfe(uint32_t v, uint32_t pos, uint32_t len) {
+  if (len == 0) return 0;
+  if (pos > 31) return 0;
+  uint64_t x = (uint64_t)v >> pos;
+  return len >= 32 ? (uint32_t)x : (uint32_t)(x & ((1ull << len) - 1ull));
+}
+inline uint32_t dp4a(uint32_t a, uint32_t b, uint32_t c) {
+  for (int i = 0; i < 4; i++) c += ((a >> (8 * i)) & 0xFFu) * ((b >> (8 * i)) & 0xFFu);
+  return c;
+}
+inline uint32_t ld_in32(const uint32_t* p) { uint32_t v; memcpy(&v, p, 4); return v; }
+inline uint8_t  ld_in8(const uint8_t* p) { return *p; }
+inline void     prefetch_l2(const void*) {}
+
+}  // namespace simt
