@@ -1,0 +1,368 @@
+#!/usr/bin/env python
+"""bench.py -- headline benchmark of the B200 inflate engine (BASELINE.json metric).
+
+Workload (N=1): BASELINE.json configs[1] -- a batch of 100 000 synthetic 64 KiB zlib streams
+(`text` payload, level 6, dynamic Huffman), decoded by one launch of the batch kernel per step.
+A "step" is one pass of the hot path over the whole batch.  N>1: every rank owns an independent
+batch of the same shape (streams shard with no collective) -> weak scaling.
+
+  value      decompressed GB/s, whole job, inputs and outputs resident in HBM (CUDA events)
+  e2e        same metric through the C ABI with HOST buffers (infl_buf_batch): H2D of the
+             compressed streams and D2H of the decoded bytes inside the timed region
+  roofline   algorithmic bytes (compressed in + decompressed out) / kernel time vs measured HBM peak
+  cpu_baseline  the reference's own infl_buf (oracle/_ref, compiled unmodified) on the host cores
+
+`--impl reference` times the reference's CPU implementation (oracle/_ref; the oracle port if the
+reference could not be compiled) on the same workload shape with all host threads.
+"""
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+import zlib
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+STREAM_BYTES = 65536
+METRIC = "decompressed GB/s, batched zlib streams"
+UNIT = "GB/s"
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--streams", type=int, default=100_000, help="streams per GPU")
+    ap.add_argument("--unique", type=int, default=8192, help="distinct streams generated on the host")
+    ap.add_argument("--lanes", type=int, default=0, help="lanes per stream (0 = engine default)")
+    ap.add_argument("--e2e-steps", type=int, default=2)
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--profile", action="store_true", help="short run for ncu: no e2e, no cpu baseline")
+    return ap.parse_args()
+
+
+# ------------------------------------------------------------------------------------------------
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        try:
+            return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+        except Exception:
+            pass
+    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+class ClockSampler(threading.Thread):
+    """SM clock and throttle reasons during the timed region (NVML; nvidia-smi semantics)."""
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.stop_flag, self.samples, self.reasons, self.max_mhz = index, False, [], set(), None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self.nv = None
+
+    def run(self):
+        if not self.nv:
+            return
+        nv = self.nv
+        names = {
+            getattr(nv, "nvmlClocksThrottleReasonHwSlowdown", 0x8): "hw_slowdown",
+            getattr(nv, "nvmlClocksThrottleReasonHwThermalSlowdown", 0x40): "hw_thermal_slowdown",
+            getattr(nv, "nvmlClocksThrottleReasonSwThermalSlowdown", 0x20): "sw_thermal_slowdown",
+            getattr(nv, "nvmlClocksThrottleReasonSwPowerCap", 0x4): "sw_power_cap",
+        }
+        while not self.stop_flag:
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for bit, name in names.items():
+                    if r & bit:
+                        self.reasons.add(name)
+            except Exception:
+                pass
+            time.sleep(0.02)
+
+    def summary(self):
+        return {"sm_mhz": float(np.median(self.samples)) if self.samples else None,
+                "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons), "samples": len(self.samples)}
+
+
+def build_pool(unique, seed0):
+    """Unique pool of config-2 streams: (raws, zlib streams)."""
+    from defl_b200 import synth
+    t0 = time.time()
+    st = synth.make_streams(synth.config2_specs(unique, size=STREAM_BYTES, first_seed=seed0),
+                            threads=os.cpu_count() or 1)
+    return [r for r, _ in st], [z for _, z in st], time.time() - t0
+
+
+# ------------------------------------------------------------------------------------------------
+def cpu_reference_run(zs, reps_min=3, budget_s=8.0, threads=None):
+    """The reference's infl_buf (oracle/_ref, else the oracle port) over the pool, all host threads.
+    -> dict for `cpu_baseline`."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import oracle_lib as ol
+    from defl_b200 import synth
+    threads = threads or (os.cpu_count() or 1)
+    n = len(zs)
+    src, so, sl = synth.pack(zs, align=1)
+    src_off = np.zeros(n + 1, dtype=np.uint64)
+    src_off[:n] = so
+    src_off[n] = so[-1] + sl[-1]
+    assert all(int(src_off[i + 1] - src_off[i]) == int(sl[i]) for i in range(n))
+    dst = np.zeros(n * STREAM_BYTES, dtype=np.uint8)
+    dst_off = (np.arange(n + 1, dtype=np.uint64) * np.uint64(STREAM_BYTES))
+    codes = np.zeros(n, dtype=np.int32)
+    kind = "reference" if ol.have_ref() else "port"
+    best, total, reps = None, 0.0, 0
+    while reps < reps_min or (total < budget_s and reps < 50):
+        if kind == "reference":
+            t = ol.ref().ref_infl_buf_batch_mt(src.ctypes.data, src_off.ctypes.data, dst.ctypes.data,
+                                               dst_off.ctypes.data, n, 1, threads, None, codes.ctypes.data)
+        else:
+            t = ol.port().oracle_inflate_batch_mt(src.ctypes.data, src_off.ctypes.data, dst.ctypes.data,
+                                                  dst_off.ctypes.data, n, 1, threads, codes.ctypes.data)
+        assert (codes == 0).all(), "CPU baseline failed to decode"
+        best = t if best is None else min(best, t)
+        total += t
+        reps += 1
+    return {"value": n * STREAM_BYTES / best / 1e9, "unit": UNIT, "cores": threads, "kind": kind,
+            "sample": f"{n} of the workload's 64 KiB streams ({n * STREAM_BYTES / 2**20:.0f} MiB out), "
+                      f"best of {reps} passes, infl_buf per stream on a pthread work queue"}, dst
+
+
+def run_reference_arm(args, rank, world):
+    if rank != 0:
+        return
+    unique = min(args.unique, 4096)
+    raws, zs, _ = build_pool(unique, 0)
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import oracle_lib as ol
+    from defl_b200 import synth
+    threads = os.cpu_count() or 1
+    n = len(zs)
+    src, so, sl = synth.pack(zs, align=1)
+    src_off = np.zeros(n + 1, dtype=np.uint64)
+    src_off[:n] = so
+    src_off[n] = so[-1] + sl[-1]
+    dst = np.zeros(n * STREAM_BYTES, dtype=np.uint8)
+    dst_off = (np.arange(n + 1, dtype=np.uint64) * np.uint64(STREAM_BYTES))
+    codes = np.zeros(n, dtype=np.int32)
+    kind = "reference" if ol.have_ref() else "port"
+
+    def step():
+        if kind == "reference":
+            return ol.ref().ref_infl_buf_batch_mt(src.ctypes.data, src_off.ctypes.data, dst.ctypes.data,
+                                                  dst_off.ctypes.data, n, 1, threads, None, codes.ctypes.data)
+        return ol.port().oracle_inflate_batch_mt(src.ctypes.data, src_off.ctypes.data, dst.ctypes.data,
+                                                 dst_off.ctypes.data, n, 1, threads, codes.ctypes.data)
+
+    for _ in range(args.warmup):
+        step()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        step()
+    dt = time.perf_counter() - t0
+    assert (codes == 0).all()
+    assert dst[:STREAM_BYTES].tobytes() == raws[0]
+    val = n * STREAM_BYTES * args.steps / dt / 1e9
+    sample = (f"each step = {n} of the workload's 64 KiB streams ({n * STREAM_BYTES / 2**20:.0f} MiB out) "
+              f"through infl_buf on {threads} host threads")
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+        "config": {"workload": "configs[1]: 64 KiB zlib streams (text, level 6, dynamic Huffman), "
+                               "reference infl_buf on host cores, bounded sample", "streams_per_step": n,
+                   "stream_bytes": STREAM_BYTES},
+        "cpu_baseline": {"value": val, "unit": UNIT, "cores": threads, "kind": kind, "sample": sample},
+        "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }))
+
+
+# ------------------------------------------------------------------------------------------------
+def main():
+    args = parse()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.profile:
+        args.no_e2e = args.no_cpu = True
+
+    if args.impl == "reference":
+        run_reference_arm(args, rank, world)
+        return
+
+    import torch
+    import torch.distributed as dist
+    import defl_b200 as d
+    from defl_b200 import synth
+
+    assert torch.cuda.is_available(), "bench.py needs a CUDA device: the engine has no CPU path"
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    d.lib()
+    if args.lanes:
+        d.set_lanes_per_stream(args.lanes)
+
+    n = args.streams
+    unique = min(args.unique, n)
+    raws, zs, gen_s = build_pool(unique, rank * 1_000_000)
+    src_h, so, sl = synth.pack(zs, align=16)
+    reps = (n + unique - 1) // unique
+    pool_bytes = int(src_h.size)
+
+    # device-resident batch: the unique pool tiled `reps` times into physically distinct memory;
+    # stream k is pool member k % unique of tile k // unique, so neighbours in launch order differ
+    t_pool = torch.from_numpy(src_h).to(dev)
+    t_src = t_pool.repeat(reps)
+    k = np.arange(n, dtype=np.int64)
+    src_off = (k // unique) * pool_bytes + so[k % unique]
+    src_len = sl[k % unique]
+    dst_off = k * STREAM_BYTES
+    dst_len = np.full(n, STREAM_BYTES, dtype=np.int64)
+    t_dst = torch.zeros(n * STREAM_BYTES, dtype=torch.uint8, device=dev)
+    batch = d.DeviceBatch(t_src, src_off, src_len, t_dst, dst_off, dst_len, order="index")
+    flags = d.INFL_ZLIB | d.INFL_BATCH_VERIFY_ADLER
+    in_bytes = int(src_len.sum())
+    out_bytes = n * STREAM_BYTES
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(max(args.warmup, 3) if not args.profile else args.warmup):
+        batch.launch(flags)
+    barrier()
+    sampler = ClockSampler(local)
+    sampler.start()
+    l0 = d.kernel_launch_count()
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps + 1)]
+    ev[0].record()
+    for i in range(args.steps):
+        batch.launch(flags)
+        ev[i + 1].record()
+    barrier()
+    sampler.stop_flag = True
+    launches = d.kernel_launch_count() - l0
+    step_ms = [ev[i].elapsed_time(ev[i + 1]) for i in range(args.steps)]
+    total_ms = ev[0].elapsed_time(ev[-1])
+    sampler.join(timeout=1.0)
+
+    # ---- byte-exact check of what was just timed: codes, Adler, tile 0 vs the generator's raw bytes,
+    #      every other tile vs tile 0 on the device
+    res = batch.results_host()
+    assert (res["code"] == 0).all(), f"decode failed: {int((res['code'] != 0).sum())} streams"
+    assert (res["outlen"] == STREAM_BYTES).all() and (res["adler"] == res["adler_stored"]).all()
+    tile0 = t_dst[: unique * STREAM_BYTES]
+    host0 = tile0.cpu().numpy()
+    for i in range(0, unique, max(1, unique // 512)):
+        assert host0[i * STREAM_BYTES:(i + 1) * STREAM_BYTES].tobytes() == raws[i], f"stream {i} differs"
+    want_adler = np.array([zlib.adler32(r) & 0xFFFFFFFF for r in raws], dtype=np.uint32)
+    assert (res["adler"][:unique] == want_adler).all()
+    for r in range(1, reps):
+        m = min(unique, n - r * unique) * STREAM_BYTES
+        assert torch.equal(t_dst[r * unique * STREAM_BYTES: r * unique * STREAM_BYTES + m], tile0[:m]), f"tile {r}"
+    del host0
+
+    t = torch.tensor([total_ms], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    total_ms_max = float(t.item())
+    value = out_bytes * world * args.steps / (total_ms_max / 1e3) / 1e9
+
+    peak, peak_src = peaks()
+    kern_ms = float(np.mean(step_ms))
+    achieved = (in_bytes + out_bytes) / (kern_ms / 1e3) / 1e9
+    roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                "traffic": None, "peak_source": peak_src, "kernel": "inflate_batch_kernel",
+                "algorithmic_bytes_per_launch": in_bytes + out_bytes,
+                "kernel_ms": kern_ms}
+    prof = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(prof):
+        try:
+            roofline["traffic"] = json.load(open(prof)).get("inflate_batch_kernel_bytes_per_launch")
+        except Exception:
+            pass
+
+    # ---- end to end through the C ABI with host buffers ------------------------------------------
+    e2e = None
+    if not args.no_e2e:
+        ne = n
+        h_src = torch.from_numpy(src_h).repeat(reps).pin_memory()
+        h_dst = torch.zeros(ne * STREAM_BYTES, dtype=torch.uint8).pin_memory()
+        items = np.zeros(ne, dtype=d.ITEM_DTYPE)
+        items["src"] = h_src.data_ptr() + src_off
+        items["srclen"] = src_len
+        items["dst"] = h_dst.data_ptr() + dst_off
+        items["dstlen"] = STREAM_BYTES
+        results = np.zeros(ne, dtype=d.RESULT_DTYPE)
+        from defl_b200 import api
+        api.infl_buf_batch_raw(items, flags, results)           # warm-up (allocates staging once)
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(args.e2e_steps):
+            api.infl_buf_batch_raw(items, flags, results)
+            assert int(results["code"][0]) == 0
+        torch.cuda.synchronize()
+        dt = time.perf_counter() - t0
+        assert (results["code"] == 0).all()
+        hv = h_dst.numpy()
+        for i in (0, unique - 1, ne - 1):
+            assert hv[i * STREAM_BYTES:(i + 1) * STREAM_BYTES].tobytes() == raws[i % unique]
+        tt = torch.tensor([dt], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        e2e = {"value": out_bytes * world * args.e2e_steps / float(tt.item()) / 1e9, "unit": UNIT,
+               "h2d_bytes_per_step": in_bytes + 36 * ne, "d2h_bytes_per_step": out_bytes + 32 * ne,
+               "steps": args.e2e_steps, "api": "infl_buf_batch (host pointers, pinned)"}
+        del h_src, h_dst
+
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu:
+        cpu, _ = cpu_reference_run(zs[: min(unique, 4096)])
+
+    if rank == 0:
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": max(args.warmup, 3) if not args.profile else args.warmup,
+            "ms_per_step": total_ms_max / args.steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+            "config": {"workload": "configs[1]: batch of 100k synthetic 64 KiB zlib streams (text, level 6, dynamic "
+                                   "Huffman), one launch per step" if n == 100_000 else
+                                   f"configs[1] shape, {n} streams per GPU",
+                       "streams_per_gpu": n, "stream_bytes": STREAM_BYTES, "unique_streams": unique,
+                       "compressed_bytes_per_gpu": in_bytes, "ratio": out_bytes / in_bytes,
+                       "l2": "inputs+outputs per step (%.1f GB) exceed L2 (126 MB); no flush needed"
+                             % ((in_bytes + out_bytes) / 1e9),
+                       "parallelism": f"{world} x independent shards, no collective",
+                       "engine": d.engine_info(), "gen_seconds": round(gen_s, 1)},
+            "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches),
+            "clocks": sampler.summary(),
+        }
+        print(json.dumps(line))
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

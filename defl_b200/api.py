@@ -265,15 +265,20 @@ class DeviceBatch:
         items[:, 2] = do + dst.data_ptr()
         items[:, 3] = dl
         self.items = items
-        if order is None:
-            order = np.argsort(-np.asarray(src_len, dtype=np.int64), kind="stable")
-        self.order = torch.as_tensor(np.asarray(order, dtype=np.int32), device=dev)
+        if isinstance(order, str) and order == "index":
+            self.order = None          # decode in index order (NULL order array)
+        else:
+            if order is None:          # largest compressed stream first keeps the tail short
+                order = np.argsort(-np.asarray(src_len, dtype=np.int64), kind="stable")
+            self.order = torch.as_tensor(np.asarray(order, dtype=np.int32), device=dev)
         self.results = torch.zeros((self.n, 32), dtype=torch.uint8, device=dev)
         self.ws = torch.zeros(int(lib().infl_batch_workspace_size(self.n)), dtype=torch.uint8, device=dev)
 
     def launch(self, flags=INFL_ZLIB):
         st = self.torch.cuda.current_stream(self.src.device).cuda_stream
-        rc = lib().infl_batch_decode_device(self.items.data_ptr(), self.order.data_ptr(), self.n, int(flags),
+        rc = lib().infl_batch_decode_device(self.items.data_ptr(),
+                                            self.order.data_ptr() if self.order is not None else None,
+                                            self.n, int(flags),
                                             self.results.data_ptr(), self.ws.data_ptr(), st)
         if rc != UNZ_OK:
             raise RuntimeError("infl_batch_decode_device: " + last_error())

@@ -1,0 +1,286 @@
+"""GPU parity tests proper: the sm_100a kernels, called through the C ABI (libdefl_b200.so), against
+the oracle (oracle/inflate_oracle.c, pinned by tests/test_oracle.py) and the committed golden
+fixtures produced by the compiled reference (tests/golden/make_golden.py).
+
+Bar: bit-exact bytes, equal produced/consumed lengths, equal return codes ({0,-1,1})."""
+import hashlib
+import zlib
+
+import numpy as np
+import pytest
+
+import oracle_lib as ol
+
+pytestmark = pytest.mark.gpu
+
+LANES = (1, 2, 4, 8, 16, 32)
+
+
+def _check_against_port(d, res, outs, datas, caps, flags, what):
+    for i, (data, cap) in enumerate(zip(datas, caps)):
+        code, out, r = ol.port_inflate(data, cap, flags)
+        g = res[i]
+        assert int(g["code"]) == code, (what, i, int(g["info"]) >> 8)
+        if code == 0:
+            assert int(g["outlen"]) == r.outlen and int(g["inpos"]) == r.inpos, (what, i)
+            assert bytes(outs[i]) == out, (what, i)
+            assert int(g["adler"]) == r.adler, (what, i)
+            assert (int(g["info"]) & 1) == r.has_trailer
+            if r.has_trailer:
+                assert int(g["adler_stored"]) == r.adler_stored
+
+
+def test_corpus_raw_every_group_width(gpu_lib, corpus):
+    """the reference's own corpus (raw deflate, flags 0), test_files.c:174-257."""
+    d = gpu_lib
+    datas = [e["data"] for e in corpus]
+    caps = [e["cap"] for e in corpus]
+    try:
+        for lanes in LANES:
+            d.set_lanes_per_stream(lanes)
+            res, outs = d.infl_buf_batch(datas, caps, 0)
+            for e, g, out in zip(corpus, res, outs):
+                assert int(g["code"]) == e["ref_code"], (e["name"], lanes, int(g["info"]) >> 8)
+                if e["ref_code"] == 0:
+                    assert int(g["outlen"]) == e["ref_outlen"], (e["name"], lanes)
+                    assert int(g["inpos"]) == e["ref_inpos"], (e["name"], lanes)
+                    assert hashlib.sha256(bytes(out)).hexdigest() == e["ref_sha256"], (e["name"], lanes)
+                if "raw_len" in e:
+                    assert int(g["adler"]) == e["raw_adler32"], (e["name"], lanes)
+    finally:
+        d.set_lanes_per_stream(0)
+
+
+def test_corpus_zlib_twins_and_adler(gpu_lib, corpus):
+    d = gpu_lib
+    es = [e for e in corpus if "raw_len" in e and e["len"]]
+    zs = [b"\x78\x9c" + e["data"] + e["raw_adler32"].to_bytes(4, "big") for e in es]
+    res, outs = d.infl_buf_batch(zs, [e["raw_len"] for e in es], d.INFL_ZLIB | d.INFL_BATCH_VERIFY_ADLER)
+    for e, z, g, out in zip(es, zs, res, outs):
+        assert int(g["code"]) == 0, e["name"]
+        assert hashlib.sha256(bytes(out)).hexdigest() == e["raw_sha256"], e["name"]
+        assert int(g["adler"]) == int(g["adler_stored"]) == e["raw_adler32"]
+        assert int(g["inpos"]) == len(z) - 4
+        assert int(g["info"]) & 3 == 3
+    # corrupt trailer: the reference's codes by default (UNZ_OK), UNZ_ERR only when verification is asked for
+    bad = [z[:-1] + bytes([z[-1] ^ 0x55]) for z in zs[:20]]
+    res, _ = d.infl_buf_batch(bad, [e["raw_len"] for e in es[:20]], d.INFL_ZLIB)
+    assert all(int(g["code"]) == 0 and (int(g["info"]) & 3) == 1 for g in res)
+    res, _ = d.infl_buf_batch(bad, [e["raw_len"] for e in es[:20]], d.INFL_ZLIB | d.INFL_BATCH_VERIFY_ADLER)
+    assert all(int(g["code"]) == -1 for g in res)
+
+
+def test_kats_through_infl_buf(gpu_lib, kats):
+    """Inline known-answer vectors of test_files.c (:468-476, :627-633) via the one-shot call."""
+    d = gpu_lib
+    for k in kats:
+        data = bytes.fromhex(k["hex"])
+        rc, out = d.infl_buf(data, k["cap"], k["flags"])
+        assert rc == k["ref_code"], k["name"]
+        if rc == 0:
+            assert bytes(out[: k["ref_outlen"]]).hex() == k["ref_out_hex"], k["name"]
+
+
+def test_reference_fuzzer_verdicts(gpu_lib, fuzz_ref):
+    """test_fuzz.c:138-246 inputs (seed 0x12345678): same verdict and bytes as the compiled reference."""
+    d = gpu_lib
+    fz = ol.RefFuzz(fuzz_ref["seed"])
+    cases = [fz.case(i) for i in range(fuzz_ref["n"])]
+    n = 1500
+    # capacity of the reference run was 1 MiB per case; outputs are tiny, so give each what it needs + slack
+    caps = [max(fuzz_ref["outlens"][i] + 64, 4096) for i in range(n)]
+    res, outs = d.infl_buf_batch(cases[:n], caps, 0)
+    for i in range(n):
+        code = fuzz_ref["codes"][i]
+        if code == 0:
+            assert int(res[i]["code"]) == 0, i
+            assert int(res[i]["outlen"]) == fuzz_ref["outlens"][i], i
+            assert hashlib.sha256(bytes(outs[i])).hexdigest()[:16] == fuzz_ref["sha16"][i], i
+        else:
+            # a failing case may fail earlier on a smaller dst, never succeed
+            assert int(res[i]["code"]) == -1, i
+
+
+def test_mutants_vs_oracle(gpu_lib):
+    """Valid, truncated, bit-flipped, over-long streams; short / exact / oversized dst; zlib and raw."""
+    from test_oracle import _mutants
+    d = gpu_lib
+    by_flag = {0: ([], []), 1: ([], [])}
+    for data, cap, flags, raw, m in _mutants(777, 2400):
+        by_flag[flags][0].append(data)
+        by_flag[flags][1].append(cap)
+    try:
+        for lanes in (1, 4, 8, 32):
+            d.set_lanes_per_stream(lanes)
+            for flags, (datas, caps) in by_flag.items():
+                res, outs = d.infl_buf_batch(datas, caps, flags)
+                _check_against_port(d, res, outs, datas, caps, flags, ("mutants", lanes, flags))
+    finally:
+        d.set_lanes_per_stream(0)
+
+
+def test_chunk_lists(gpu_lib, corpus):
+    """infl_init + N x infl_include + infl, piece sizes 1,2,4,8 cycling (test_files.c:260-331)."""
+    d = gpu_lib
+    names = {"hello", "hello_world", "json", "html", "text_repeated", "zeros_1k", "repeated_a_258", "ascii",
+             "huffman_single_a", "distance_test_1", "length_test_3", "bit_align_7",       # test_files.c:1037-1041
+             "png_simulation", "multi_block_1", "uncompressed_medium"}
+    picked = [e for e in corpus if e["name"] in names and "raw_len" in e]
+    assert len(picked) >= 12
+    for e in picked:
+        data = e["data"]
+        st = d.InflStream(e["cap"], 0)
+        pos = k = 0
+        while pos < len(data):
+            n = 1 << (k % 4)
+            st.include(data[pos:pos + n])
+            pos += n
+            k += 1
+        assert st.infl() == d.UNZ_OK, e["name"]
+        assert st.output_pos() == e["raw_len"]
+        assert hashlib.sha256(bytes(st.output())).hexdigest() == e["raw_sha256"], e["name"]
+        assert st.input_pos() == e["ref_inpos"]
+        st.destroy()
+    st = d.InflStream(16, 0)
+    assert st.infl() == d.UNZ_NOOP
+    st.include(b"")
+    st.include(b"")
+    assert st.infl() == d.UNZ_OK and st.output_pos() == 0
+    st.destroy()
+
+
+def test_chunk_lists_batch_iov_large(gpu_lib):
+    """BASELINE.json configs[2] shape at reduced size: streams split into 1 B .. 32 KiB pieces."""
+    from defl_b200 import synth
+    d = gpu_lib
+    streams = synth.make_streams([("png", 1 << 20, 1, 6, zlib.Z_DEFAULT_STRATEGY),
+                                  ("text", 1 << 20, 2, 6, zlib.Z_DEFAULT_STRATEGY),
+                                  ("rand", 300000, 3, 6, zlib.Z_DEFAULT_STRATEGY)])
+    s = 0x12345678
+    lists = []
+    for raw, z in streams:
+        pieces, pos = [], 0
+        while pos < len(z):
+            s = (s * 1103515245 + 12345) & 0xFFFFFFFF
+            n = 1 + (s >> 8) % 16 if (s >> 4) & 1 else 1 + (s >> 8) % 32768
+            pieces.append(z[pos:pos + n])
+            pos += n
+        lists.append(pieces)
+    res, outs = d.infl_buf_batch_iov(lists, [len(r) for r, _ in streams], d.INFL_ZLIB | d.INFL_BATCH_VERIFY_ADLER)
+    for (raw, z), g, out in zip(streams, res, outs):
+        assert int(g["code"]) == 0 and bytes(out) == raw
+        assert int(g["adler"]) == (zlib.adler32(raw) & 0xFFFFFFFF)
+
+
+def test_infl_stream_shim(gpu_lib, corpus):
+    """infl_stream(): UNZ_UNFINISHED until the final block is in, then UNZ_OK (test_files.c:688-790);
+    UNZ_EFULL + infl_resize_output resumes (stream.c:614-627, mem.c:277-288)."""
+    d = gpu_lib
+    names = {"hello", "hello_world", "json", "zeros_1k", "huffman_single_a", "multi_block_1",
+             "dynamic_huffman_1", "distance_test_1", "length_test_3", "bit_align_7", "png_simulation"}
+    for e in [x for x in corpus if x["name"] in names and "raw_len" in x]:      # test_files.c:1043-1048
+        data = e["data"]
+        st = d.InflStream(e["cap"], 0)
+        rc, pos, k = d.UNZ_UNFINISHED, 0, 0
+        while pos < len(data):
+            n = 64 << (k % 5)
+            rc = st.stream(data[pos:pos + n])
+            pos += n
+            k += 1
+            if rc != d.UNZ_UNFINISHED:
+                break
+        assert rc == d.UNZ_OK, e["name"]
+        assert hashlib.sha256(bytes(st.output())).hexdigest() == e["raw_sha256"], e["name"]
+        st.destroy()
+    e = next(x for x in corpus if x["name"] == "png_simulation")
+    data = e["data"]
+    st = d.InflStream(e["raw_len"] // 2, 0)
+    assert st.stream(data) == d.UNZ_EFULL
+    assert st.resize_output(e["raw_len"]) == d.UNZ_OK
+    assert st.stream(None) == d.UNZ_OK
+    assert hashlib.sha256(bytes(st.output())).hexdigest() == e["raw_sha256"]
+    st.destroy()
+
+
+def test_edge_shapes(gpu_lib):
+    """Longest match, farthest distance, overlapping short periods, empty/ragged batch members."""
+    d = gpu_lib
+    rnd = np.random.default_rng(5)
+    raws = [
+        b"",                                                    # empty payload, valid stream
+        b"a",
+        b"ab" * 40000,                                           # period 2, len 258 matches
+        b"abc" * 30000, b"abcde" * 20000, b"abcdefg" * 12000,    # short periods < 8
+        bytes(rnd.integers(0, 256, 32768, dtype=np.uint8)) * 3,  # distance 32768
+        bytes(rnd.integers(0, 4, 70000, dtype=np.uint8)),        # short codes, dense matches
+        b"\0" * 500000,
+    ]
+    datas, caps = [], []
+    for raw in raws:
+        for level, strat in ((6, zlib.Z_DEFAULT_STRATEGY), (9, zlib.Z_DEFAULT_STRATEGY), (1, zlib.Z_FIXED),
+                             (0, zlib.Z_DEFAULT_STRATEGY), (6, zlib.Z_HUFFMAN_ONLY), (6, zlib.Z_RLE)):
+            c = zlib.compressobj(level, zlib.DEFLATED, 15, 8, strat)
+            datas.append(c.compress(raw) + c.flush())
+            caps.append(len(raw))
+    try:
+        for lanes in LANES:
+            d.set_lanes_per_stream(lanes)
+            res, outs = d.infl_buf_batch(datas, caps, d.INFL_ZLIB)
+            _check_against_port(d, res, outs, datas, caps, 1, ("edges", lanes))
+            for i, out in enumerate(outs):
+                assert bytes(out) == raws[i // 6]
+    finally:
+        d.set_lanes_per_stream(0)
+    # an empty batch and NULL-sized members
+    res, outs = d.infl_buf_batch([b"", zlib.compress(b"xyz")], [4, 3], d.INFL_ZLIB)
+    assert int(res[0]["code"]) == 0 and int(res[0]["outlen"]) == 0 and bytes(outs[1]) == b"xyz"
+
+
+def test_config2_reduced_and_device_resident(gpu_lib):
+    """BASELINE.json configs[1] at a size the oracle finishes in seconds: 64 KiB text streams, level 6,
+    device-resident batch through infl_batch_decode_device, compared with the oracle byte for byte."""
+    import torch
+    from defl_b200 import synth
+    d = gpu_lib
+    n = 600
+    streams = synth.make_streams(synth.config2_specs(n, first_seed=10_000))
+    zs = [z for _, z in streams]
+    src, so, sl = synth.pack(zs)
+    dl = np.full(n, 65536, dtype=np.int64)
+    do = np.arange(n, dtype=np.int64) * 65536
+    tsrc = torch.from_numpy(src).cuda()
+    tdst = torch.zeros(n * 65536, dtype=torch.uint8, device="cuda")
+    b = d.DeviceBatch(tsrc, so, sl, tdst, do, dl)
+    b.launch(d.INFL_ZLIB | d.INFL_BATCH_VERIFY_ADLER)
+    torch.cuda.synchronize()
+    res = b.results_host()
+    out = tdst.cpu().numpy()
+    for i, (raw, z) in enumerate(streams):
+        code, o, r = ol.port_inflate(z, 65536, 1)
+        assert code == 0 and int(res[i]["code"]) == 0
+        assert int(res[i]["adler"]) == r.adler == int(res[i]["adler_stored"])
+        assert out[i * 65536:(i + 1) * 65536].tobytes() == o == raw
+
+
+def test_gather_kernel(gpu_lib):
+    """K2: descriptor-driven gather, every alignment and tiny lengths (reference mem.c:121-155 joins on the host)."""
+    import torch
+    d = gpu_lib
+    rnd = np.random.default_rng(11)
+    blob = rnd.integers(0, 256, 1 << 20, dtype=np.uint8)
+    tb = torch.from_numpy(blob).cuda()
+    lens = np.concatenate([rnd.integers(0, 40, 3000), rnd.integers(0, 70000, 40)]).astype(np.uint64)
+    srcoff = rnd.integers(0, (1 << 20) - 70000, lens.size).astype(np.uint64)
+    dstoff = np.zeros(lens.size, dtype=np.uint64)
+    dstoff[1:] = np.cumsum(lens)[:-1]
+    total = int(lens.sum())
+    out = torch.zeros(total + 16, dtype=torch.uint8, device="cuda")
+    t_src = torch.from_numpy((srcoff + np.uint64(tb.data_ptr())).astype(np.int64)).cuda()
+    t_len = torch.from_numpy(lens.astype(np.int64)).cuda()
+    t_off = torch.from_numpy(dstoff.astype(np.int64)).cuda()
+    rc = d.lib().infl_gather_device(t_src.data_ptr(), t_len.data_ptr(), t_off.data_ptr(), lens.size,
+                                    out.data_ptr(), torch.cuda.current_stream().cuda_stream)
+    assert rc == 0
+    torch.cuda.synchronize()
+    want = np.concatenate([blob[int(o):int(o) + int(n)] for o, n in zip(srcoff, lens)])
+    assert np.array_equal(out.cpu().numpy()[:total], want)
