@@ -32,7 +32,7 @@ thread_local std::string      g_last_error;
 std::atomic<uint64_t>         g_launches{0};
 std::atomic<int>              g_lanes_per_stream{0};
 
-constexpr int kDefaultLanes = 8;
+constexpr int kDefaultLanes = 32;
 
 int fail(const char* what, cudaError_t e = cudaSuccess) {
   g_last_error = what;

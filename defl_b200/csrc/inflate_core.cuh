@@ -74,9 +74,8 @@ DEFL_DEV uint32_t cl_order(uint32_t i) {
   return i < 12u ? (uint32_t)(kClOrderLo >> (5u * i)) & 31u : (uint32_t)(kClOrderHi >> (5u * (i - 12u))) & 31u;
 }
 
-struct GroupSmem {
-  uint16_t lit[kLitTab];
-  uint16_t dist[kDistTab];
+// scratch needed only while a block header is parsed and its tables are built
+struct BuildScratch {
   uint8_t  lens[320];     // code lengths of the current dynamic block (HLIT + HDIST)
   uint8_t  cltab[128];    // 7-bit lookup for the code-length code: sym << 3 | bits
   uint32_t cnt[16];       // codes per length
@@ -84,6 +83,12 @@ struct GroupSmem {
   uint16_t sub_lo[16];    // per length > root: first root prefix that holds such codes
   uint16_t sub_base[16];  // per length > root: table offset of that prefix's sub-table
   uint8_t  cl[32];        // the 19 code-length-code lengths
+};
+
+struct GroupSmem {
+  uint16_t     lit[kLitTab];
+  uint16_t     dist[kDistTab];
+  BuildScratch s;
 };
 
 struct StreamOut {
@@ -240,7 +245,7 @@ DEFL_DEV uint32_t dist_entry(uint32_t sym, uint32_t len) {
 // Build one decode table from code lengths.  Accept/reject exactly as infl_ft_build
 // (infl.c:478-490): over-subscribed => false; incomplete or empty => true.
 template <int G, int ROOT_BITS, int TAB, bool IS_DIST>
-DEFL_DEV bool build_table(const Lane<G>& L, GroupSmem& sm, uint16_t* tab, const uint8_t* lens,
+DEFL_DEV bool build_table(const Lane<G>& L, BuildScratch& sm, uint16_t* tab, const uint8_t* lens,
                           uint32_t n) {
   constexpr uint32_t ROOT = 1u << ROOT_BITS;
 
@@ -332,7 +337,7 @@ DEFL_DEV bool build_table(const Lane<G>& L, GroupSmem& sm, uint16_t* tab, const 
 
 // 7-bit lookup for the code-length code (19 symbols, lengths 0..7).  Over-subscribed => false.
 template <int G>
-DEFL_DEV bool build_cl_table(const Lane<G>& L, GroupSmem& sm) {
+DEFL_DEV bool build_cl_table(const Lane<G>& L, BuildScratch& sm) {
   uint64_t cnt = 0;
   for (int i = 0; i < 19; i++) cnt += 1ull << (8 * sm.cl[i]);
   cnt &= ~0xFFull;
@@ -364,7 +369,162 @@ DEFL_DEV bool build_cl_table(const Lane<G>& L, GroupSmem& sm) {
   return true;
 }
 
-// ---- one stream ---------------------------------------------------------------------------------------
+
+// ---- block pieces shared by the group-per-stream kernel and the lane-decoder pipeline ---------------
+
+// Stored block (infl_ft_stored, infl.c:659-715).  `br` stands right after the 3 header bits.
+// Copies into dst[pos..), advances pos and re-seeks br.  Returns a Reason.
+template <int G>
+DEFL_DEV uint32_t stored_block(const Lane<G>& L, BitReader& br, const uint8_t* src, uint32_t srclen,
+                               uint64_t base_bit, uint8_t* dst, uint32_t& pos, uint32_t cap) {
+  const uint64_t bytepos = ((br.bitpos() - base_bit) + 7u) >> 3;  // from src[0]
+  if (bytepos + 4u > srclen) return R_TRUNCATED;
+  const uint8_t* p = src + bytepos;
+  const uint32_t len  = simt::ld_in8(p) | ((uint32_t)simt::ld_in8(p + 1) << 8);
+  const uint32_t nlen = simt::ld_in8(p + 2) | ((uint32_t)simt::ld_in8(p + 3) << 8);
+  if ((len ^ (~nlen & 0xFFFFu)) != 0u) return R_STORED_LEN;
+  if (len > cap - pos) return R_OUTPUT_FULL;
+  if ((uint64_t)len > srclen - bytepos - 4u) return R_TRUNCATED;
+  simt::syncwarp(L.gmask);
+  copy_from_input<G>(L, dst + pos, p + 4, len);
+  simt::syncwarp(L.gmask);
+  pos += len;
+  br.seek(base_bit + (bytepos + 4u + len) * 8u);
+  return R_NONE;
+}
+
+// Fixed (btype 1) or dynamic (btype 2) block: leave decode tables for it in lit/dist.
+// `br` stands right after the 3 header bits.  Returns a Reason.
+template <int G>
+DEFL_DEV uint32_t huffman_block_setup(const Lane<G>& L, uint16_t* lit, uint16_t* dist, BuildScratch& s,
+                                      BitReader& br, uint64_t end_bit, uint32_t btype, bool& fixed_ready) {
+  if (btype == 1) {
+    if (!fixed_ready) {
+      // fixed code lengths (RFC 1951 3.2.6; reference table fxd, apicommon.h:53-64)
+      simt::syncwarp(L.gmask);
+      for (uint32_t i = L.lane; i < 320u; i += G)
+        s.lens[i] = i < 144u ? 8 : i < 256u ? 9 : i < 280u ? 7 : i < 288u ? 8 : 5;
+      simt::syncwarp(L.gmask);
+      build_table<G, kLitRootBits, kLitTab, false>(L, s, lit, s.lens, 288u);
+      build_table<G, kDistRootBits, kDistTab, true>(L, s, dist, s.lens + 288, 32u);
+      fixed_ready = true;
+    }
+    return R_NONE;
+  }
+  // ---- dynamic header (infl_ft_dynamic, infl.c:903-1000)
+  fixed_ready = false;
+  int64_t rem = (int64_t)(end_bit - br.bitpos());
+  if (rem < 14) return R_TRUNCATED;
+  uint32_t v = br.peek();
+  const uint32_t hlit = (v & 31u) + 257u, hdist = ((v >> 5) & 31u) + 1u, hclen = ((v >> 10) & 15u) + 4u;
+  const uint32_t n = hlit + hdist;
+  br.skip(14); br.norm();
+  rem -= 14;
+  if (rem < (int64_t)(3u * hclen)) return R_TRUNCATED;
+  simt::syncwarp(L.gmask);
+  if (L.lane == 0) {
+    for (int i = 0; i < 20; i++) s.cl[i] = 0;
+  }
+  for (uint32_t i = L.lane; i < 80u; i += G) reinterpret_cast<uint32_t*>(s.lens)[i] = 0u;
+  simt::syncwarp(L.gmask);
+  for (uint32_t i = 0; i < hclen; i++) {
+    const uint32_t v3 = br.peek() & 7u;
+    br.skip(3); br.norm();
+    if (L.lane == 0) s.cl[cl_order(i)] = (uint8_t)v3;
+  }
+  rem -= 3 * (int64_t)hclen;
+  simt::syncwarp(L.gmask);
+  if (!build_cl_table<G>(L, s)) return R_CODE_LENGTHS;
+
+  uint32_t i = 0, prev = 0, reason = R_NONE;
+#pragma unroll 1
+  while (i < n) {
+    if (rem < 7) { reason = R_TRUNCATED; break; }       // infl.c:946-948
+    v = br.peek();
+    const uint32_t e = s.cltab[v & 127u];
+    if (!e) { reason = R_CODE_LENGTHS; break; }         // infl.c:951-952
+    const uint32_t l = e & 7u, sym = e >> 3;
+    uint32_t used = l;
+    v >>= l;
+    if (sym < 16u) {
+      if (L.lane == 0) s.lens[i] = (uint8_t)sym;
+      prev = sym;
+      i++;
+    } else {
+      uint32_t rep, xb;
+      if (sym == 16u)      { xb = 2; rep = 3u + (v & 3u); }
+      else if (sym == 17u) { xb = 3; rep = 3u + (v & 7u); }
+      else                 { xb = 7; rep = 11u + (v & 127u); }
+      if (rem - (int64_t)l < (int64_t)xb || (sym == 16u && i == 0u) || i + rep > n) {
+        reason = (rem - (int64_t)l < (int64_t)xb) ? R_TRUNCATED : R_CODE_LENGTHS;  // infl.c:960-985
+        break;
+      }
+      used += xb;
+      if (sym == 16u) {
+        for (uint32_t k = L.lane; k < rep; k += G) s.lens[i + k] = (uint8_t)prev;
+      } else {
+        prev = 0;
+      }
+      i += rep;
+    }
+    br.skip(used); br.norm();
+    rem -= used;
+  }
+  if (reason) return reason;
+  simt::syncwarp(L.gmask);
+  if (!build_table<G, kLitRootBits, kLitTab, false>(L, s, lit, s.lens, hlit) ||
+      !build_table<G, kDistRootBits, kDistTab, true>(L, s, dist, s.lens + hlit, hdist))
+    return R_TABLE;
+  return R_NONE;
+}
+
+// zlib header (infl.c:1027-1039, zlib.h:45-96).  Returns a Reason; body = bytes to skip.
+DEFL_DEV uint32_t zlib_header(const uint8_t* src, uint32_t srclen, uint32_t& body) {
+  body = 0;
+  if (srclen < 2) return R_TRUNCATED;
+  const uint32_t cmf = simt::ld_in8(src), flg = simt::ld_in8(src + 1);
+  if ((cmf & 15u) != 8u || (cmf >> 4) > 7u || ((cmf << 8) + flg) % 31u != 0u || (flg & 0x20u)) return R_ZLIB_HEADER;
+  body = 2;
+  return R_NONE;
+}
+
+// A symbol-level failure met at or beyond the end of the input is a truncation first: the symbol
+// that ran off the end precedes it in stream order (matters to infl_stream() only).
+DEFL_DEV uint32_t settle_reason(uint32_t reason, int64_t avail_bits) {
+  if (avail_bits < 0 || ((reason == R_SYMBOL || reason == R_DISTANCE) && avail_bits < 15)) return R_TRUNCATED;
+  return reason;
+}
+
+// Result record of a stream that decoded to its final block: Adler-32 from the partial sums,
+// consumed bytes (mem.c:296-329), the stored trailer and the optional verification.
+template <int G>
+DEFL_DEV void finish_stream(const Lane<G>& L, const uint8_t* src, uint32_t srclen, uint32_t pos,
+                            uint64_t consumed_bits, uint32_t A, uint32_t W, bool zlib, int flags, StreamOut& out) {
+  const uint32_t sa = group_sum<G>(L, A) % kAdlerMod;
+  const uint32_t sw = group_sum<G>(L, W) % kAdlerMod;
+  const uint32_t nm = pos % kAdlerMod;
+  const uint32_t a  = (1u + sa) % kAdlerMod;
+  const uint32_t b  = (uint32_t)((nm + (uint64_t)nm * sa + kAdlerMod - sw) % kAdlerMod);
+  out.adler  = (b << 16) | a;
+  out.outlen = pos;
+  out.inpos  = (uint32_t)((consumed_bits + 7u) >> 3);
+  out.code   = 0;
+  out.adler_stored = 0;
+  out.info = 0;
+  if (zlib && srclen - out.inpos >= 4u) {
+    const uint8_t* t = src + out.inpos;
+    out.adler_stored = ((uint32_t)simt::ld_in8(t) << 24) | ((uint32_t)simt::ld_in8(t + 1) << 16) |
+                       ((uint32_t)simt::ld_in8(t + 2) << 8) | simt::ld_in8(t + 3);
+    out.info |= 1u;                                   // INFL_INFO_HAS_TRAILER
+    if (out.adler_stored == out.adler) out.info |= 2u; // INFL_INFO_ADLER_MATCH
+  }
+  if (zlib && (flags & 0x0100) && (out.info & 3u) != 3u) {  // INFL_BATCH_VERIFY_ADLER
+    out.code = -1;
+    out.info |= R_ADLER << 8;
+  }
+}
+
+// ---- one stream, decoded start to finish by one group of G lanes -------------------------------------
 template <int G>
 DEFL_DEV void inflate_stream(const Lane<G>& L, GroupSmem& sm, const uint8_t* src, uint32_t srclen,
                              uint8_t* dst, uint32_t cap, int flags, StreamOut& out) {
@@ -375,14 +535,9 @@ DEFL_DEV void inflate_stream(const Lane<G>& L, GroupSmem& sm, const uint8_t* src
 
   const bool zlib = (flags & 0xFF) == 1;
   uint32_t   body = 0;
-  if (zlib) {                                         // infl.c:1027-1039, zlib.h:45-96
-    if (srclen < 2) { out.info = R_TRUNCATED << 8; return; }
-    const uint32_t cmf = simt::ld_in8(src), flg = simt::ld_in8(src + 1);
-    if ((cmf & 15u) != 8u || (cmf >> 4) > 7u || ((cmf << 8) + flg) % 31u != 0u || (flg & 0x20u)) {
-      out.info = R_ZLIB_HEADER << 8;
-      return;
-    }
-    body = 2;
+  if (zlib) {
+    const uint32_t hr = zlib_header(src, srclen, body);
+    if (hr) { out.info = hr << 8; return; }
   }
 
   const uint32_t mis      = (uint32_t)((uintptr_t)src & 3u);
@@ -400,109 +555,20 @@ DEFL_DEV void inflate_stream(const Lane<G>& L, GroupSmem& sm, const uint8_t* src
 #pragma unroll 1
   for (;;) {
     // ---- block header (infl.c:1063-1070)
-    int64_t rem = (int64_t)(end_bit - br.bitpos());
-    if (rem < 3) { reason = R_TRUNCATED; break; }
+    if ((int64_t)(end_bit - br.bitpos()) < 3) { reason = R_TRUNCATED; break; }
     const uint32_t hdr    = br.peek();
     const uint32_t bfinal = hdr & 1u, btype = (hdr >> 1) & 3u;
     br.skip(3); br.norm();
 
     if (btype == 0) {
-      // ---- stored (infl_ft_stored, infl.c:659-715)
-      const uint64_t bytepos = ((br.bitpos() - base_bit) + 7u) >> 3;  // from src[0]
-      if (bytepos + 4u > srclen) { reason = R_TRUNCATED; break; }
-      const uint8_t* p = src + bytepos;
-      const uint32_t len  = simt::ld_in8(p) | ((uint32_t)simt::ld_in8(p + 1) << 8);
-      const uint32_t nlen = simt::ld_in8(p + 2) | ((uint32_t)simt::ld_in8(p + 3) << 8);
-      if ((len ^ (~nlen & 0xFFFFu)) != 0u) { reason = R_STORED_LEN; break; }
-      if (len > cap - pos) { reason = R_OUTPUT_FULL; break; }
-      if ((uint64_t)len > srclen - bytepos - 4u) { reason = R_TRUNCATED; break; }
-      simt::syncwarp(L.gmask);
-      copy_from_input<G>(L, dst + pos, p + 4, len);
-      simt::syncwarp(L.gmask);
-      pos += len;
-      br.seek(base_bit + (bytepos + 4u + len) * 8u);
+      reason = stored_block<G>(L, br, src, srclen, base_bit, dst, pos, cap);
+      if (reason) break;
     } else if (btype == 3) {
       reason = R_BLOCK_TYPE;
       break;
     } else {
-      if (btype == 1) {
-        if (!fixed_ready) {
-          // fixed code lengths (RFC 1951 3.2.6; reference table fxd, apicommon.h:53-64)
-          simt::syncwarp(L.gmask);
-          for (uint32_t i = L.lane; i < 320u; i += G)
-            sm.lens[i] = i < 144u ? 8 : i < 256u ? 9 : i < 280u ? 7 : i < 288u ? 8 : 5;
-          simt::syncwarp(L.gmask);
-          build_table<G, kLitRootBits, kLitTab, false>(L, sm, sm.lit, sm.lens, 288u);
-          build_table<G, kDistRootBits, kDistTab, true>(L, sm, sm.dist, sm.lens + 288, 32u);
-          fixed_ready = true;
-        }
-      } else {
-        // ---- dynamic header (infl_ft_dynamic, infl.c:903-1000)
-        fixed_ready = false;
-        if (rem - 3 < 14) { reason = R_TRUNCATED; break; }
-        uint32_t v = br.peek();
-        const uint32_t hlit = (v & 31u) + 257u, hdist = ((v >> 5) & 31u) + 1u, hclen = ((v >> 10) & 15u) + 4u;
-        const uint32_t n = hlit + hdist;
-        br.skip(14); br.norm();
-        rem -= 17;
-        if (rem < (int64_t)(3u * hclen)) { reason = R_TRUNCATED; break; }
-        simt::syncwarp(L.gmask);
-        if (L.lane == 0) {
-          for (int i = 0; i < 20; i++) sm.cl[i] = 0;
-        }
-        for (uint32_t i = L.lane; i < 80u; i += G) reinterpret_cast<uint32_t*>(sm.lens)[i] = 0u;
-        simt::syncwarp(L.gmask);
-        for (uint32_t i = 0; i < hclen; i++) {
-          const uint32_t v3 = br.peek() & 7u;
-          br.skip(3); br.norm();
-          if (L.lane == 0) sm.cl[cl_order(i)] = (uint8_t)v3;
-        }
-        rem -= 3 * (int64_t)hclen;
-        simt::syncwarp(L.gmask);
-        if (!build_cl_table<G>(L, sm)) { reason = R_CODE_LENGTHS; break; }
-
-        uint32_t i = 0, prev = 0;
-#pragma unroll 1
-        while (i < n) {
-          if (rem < 7) { reason = R_TRUNCATED; break; }       // infl.c:946-948
-          v = br.peek();
-          const uint32_t e = sm.cltab[v & 127u];
-          if (!e) { reason = R_CODE_LENGTHS; break; }         // infl.c:951-952
-          const uint32_t l = e & 7u, sym = e >> 3;
-          uint32_t used = l;
-          v >>= l;
-          if (sym < 16u) {
-            if (L.lane == 0) sm.lens[i] = (uint8_t)sym;
-            prev = sym;
-            i++;
-          } else {
-            uint32_t rep, xb;
-            if (sym == 16u)      { xb = 2; rep = 3u + (v & 3u); }
-            else if (sym == 17u) { xb = 3; rep = 3u + (v & 7u); }
-            else                 { xb = 7; rep = 11u + (v & 127u); }
-            if (rem - (int64_t)l < (int64_t)xb || (sym == 16u && i == 0u) || i + rep > n) {
-              reason = (rem - (int64_t)l < (int64_t)xb) ? R_TRUNCATED : R_CODE_LENGTHS;  // infl.c:960-985
-              break;
-            }
-            used += xb;
-            if (sym == 16u) {
-              for (uint32_t k = L.lane; k < rep; k += G) sm.lens[i + k] = (uint8_t)prev;
-            } else {
-              prev = 0;
-            }
-            i += rep;
-          }
-          br.skip(used); br.norm();
-          rem -= used;
-        }
-        if (reason) break;
-        simt::syncwarp(L.gmask);
-        if (!build_table<G, kLitRootBits, kLitTab, false>(L, sm, sm.lit, sm.lens, hlit) ||
-            !build_table<G, kDistRootBits, kDistTab, true>(L, sm, sm.dist, sm.lens + hlit, hdist)) {
-          reason = R_TABLE;
-          break;
-        }
-      }
+      reason = huffman_block_setup<G>(L, sm.lit, sm.dist, sm.s, br, end_bit, btype, fixed_ready);
+      if (reason) break;
 
       // ---- symbols (infl_ft_block, infl.c:717-901)
 #pragma unroll 1
@@ -554,10 +620,7 @@ DEFL_DEV void inflate_stream(const Lane<G>& L, GroupSmem& sm, const uint8_t* src
         pos += len;
       }
       if (reason) {
-        // a failure met at or beyond the end of the input is a truncation first: the symbol that
-        // ran off the end precedes it in stream order (matters to infl_stream() only)
-        const int64_t avail = (int64_t)(end_bit - br.bitpos());
-        if (avail < 0 || ((reason == R_SYMBOL || reason == R_DISTANCE) && avail < 15)) reason = R_TRUNCATED;
+        reason = settle_reason(reason, (int64_t)(end_bit - br.bitpos()));
         break;
       }
       // the reference fails a symbol whose bits are not all there (infl.c:741-745,806-810);
@@ -572,27 +635,7 @@ DEFL_DEV void inflate_stream(const Lane<G>& L, GroupSmem& sm, const uint8_t* src
   }
 
   if (reason) { out.info = reason << 8; out.outlen = pos; return; }
-
-  const uint32_t sa = group_sum<G>(L, A) % kAdlerMod;
-  const uint32_t sw = group_sum<G>(L, W) % kAdlerMod;
-  const uint32_t nm = pos % kAdlerMod;
-  const uint32_t a  = (1u + sa) % kAdlerMod;
-  const uint32_t b  = (uint32_t)((nm + (uint64_t)nm * sa + kAdlerMod - sw) % kAdlerMod);
-  out.adler  = (b << 16) | a;
-  out.outlen = pos;
-  out.inpos  = (uint32_t)(((br.bitpos() - base_bit) + 7u) >> 3);   // mem.c:296-329
-  out.code   = 0;
-  if (zlib && srclen - out.inpos >= 4u) {
-    const uint8_t* t = src + out.inpos;
-    out.adler_stored = ((uint32_t)simt::ld_in8(t) << 24) | ((uint32_t)simt::ld_in8(t + 1) << 16) |
-                       ((uint32_t)simt::ld_in8(t + 2) << 8) | simt::ld_in8(t + 3);
-    out.info |= 1u;                                   // INFL_INFO_HAS_TRAILER
-    if (out.adler_stored == out.adler) out.info |= 2u; // INFL_INFO_ADLER_MATCH
-  }
-  if (zlib && (flags & 0x0100) && (out.info & 3u) != 3u) {  // INFL_BATCH_VERIFY_ADLER
-    out.code = -1;
-    out.info |= R_ADLER << 8;
-  }
+  finish_stream<G>(L, src, srclen, pos, br.bitpos() - base_bit, A, W, zlib, flags, out);
 }
 
 }  // namespace defl
