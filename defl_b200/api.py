@@ -38,7 +38,7 @@ EXPORTED_SYMBOLS = [
     "infl_buf_batch", "infl_buf_batch_iov", "infl_batch_workspace_size", "infl_batch_decode_device",
     "infl_gather_device",
     "infl_device_count", "infl_last_error", "infl_engine_info",
-    "infl_kernel_launch_count", "infl_set_lanes_per_stream",
+    "infl_kernel_launch_count", "infl_set_lanes_per_stream", "infl_set_pipeline_shape",
 ]
 
 _lib = None
@@ -95,6 +95,8 @@ def lib():
     L.infl_kernel_launch_count.restype = u64
     L.infl_set_lanes_per_stream.restype = i32
     L.infl_set_lanes_per_stream.argtypes = [i32]
+    L.infl_set_pipeline_shape.restype = i32
+    L.infl_set_pipeline_shape.argtypes = [i32]
     _lib = L
     return L
 
@@ -113,6 +115,11 @@ def kernel_launch_count():
 
 def set_lanes_per_stream(lanes):
     if lib().infl_set_lanes_per_stream(int(lanes)) != UNZ_OK:
+        raise ValueError(last_error())
+
+
+def set_pipeline_shape(shape):
+    if lib().infl_set_pipeline_shape(int(shape)) != UNZ_OK:
         raise ValueError(last_error())
 
 

@@ -32,7 +32,6 @@ thread_local std::string      g_last_error;
 std::atomic<uint64_t>         g_launches{0};
 std::atomic<int>              g_lanes_per_stream{0};
 
-constexpr int kDefaultLanes = 32;
 
 int fail(const char* what, cudaError_t e = cudaSuccess) {
   g_last_error = what;
@@ -144,13 +143,53 @@ int launch_batch(int sms, const infl_batch_item_t* d_items, const uint32_t* d_or
   return UNZ_OK;
 }
 
+std::atomic<int> g_pipeline_shape{0};
+
+template <int D, int SL, int K>
+int launch_pipeline(int sms, const infl_batch_item_t* d_items, const uint32_t* d_order, uint32_t n, int flags,
+                    infl_batch_result_t* d_results, unsigned int* d_ticket, cudaStream_t st) {
+  auto             kern = defl::inflate_pipeline_kernel<D, SL, K>;
+  constexpr size_t smem = defl::pipeline_smem_bytes<D, SL, K>();
+  static int       ctas_per_sm[kMaxDevices] = {0};
+  int              dev = 0;
+  cudaGetDevice(&dev);
+  if (!ctas_per_sm[dev]) {
+    CU_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem),
+           "cudaFuncSetAttribute(smem)");
+    int occ = 0;
+    CU_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, (D + K) * 32, smem), "occupancy query");
+    if (occ < 1) return fail("inflate pipeline kernel does not fit on an SM");
+    ctas_per_sm[dev] = occ;
+  }
+  uint64_t grid = (uint64_t)sms * ctas_per_sm[dev];
+  grid = std::min<uint64_t>(grid, (n + D * SL - 1) / (D * SL));
+  grid = std::max<uint64_t>(grid, 1);
+  CU_TRY(cudaMemsetAsync(d_ticket, 0, sizeof(unsigned int), st), "cudaMemsetAsync(ticket)");
+  kern<<<(unsigned)grid, (D + K) * 32, smem, st>>>(d_items, d_order, n, flags, d_results, d_ticket);
+  CU_TRY(cudaGetLastError(), "inflate_pipeline_kernel launch");
+  g_launches.fetch_add(1, std::memory_order_relaxed);
+  return UNZ_OK;
+}
+
 int launch_batch_any(int sms, const infl_batch_item_t* d_items, const uint32_t* d_order, size_t n, int flags,
                      infl_batch_result_t* d_results, void* d_ws, cudaStream_t st) {
   if (n == 0) return UNZ_OK;
   if (n > 0xFFFFFFFFull) return fail("batch too large (n must fit 32 bits)");
   int  lanes = g_lanes_per_stream.load();
-  if (!lanes) lanes = kDefaultLanes;
   auto t = static_cast<unsigned int*>(d_ws);
+  if (!lanes) {   // default: the lane-decoder pipeline (v2)
+    switch (g_pipeline_shape.load()) {
+      case 0:  return launch_pipeline<2, 24, 14>(sms, d_items, d_order, (uint32_t)n, flags, d_results, t, st);
+      case 1:  return launch_pipeline<2, 24, 8>(sms, d_items, d_order, (uint32_t)n, flags, d_results, t, st);
+      case 2:  return launch_pipeline<3, 16, 10>(sms, d_items, d_order, (uint32_t)n, flags, d_results, t, st);
+      case 3:  return launch_pipeline<4, 12, 10>(sms, d_items, d_order, (uint32_t)n, flags, d_results, t, st);
+      case 4:  return launch_pipeline<6, 8, 10>(sms, d_items, d_order, (uint32_t)n, flags, d_results, t, st);
+      case 5:  return launch_pipeline<12, 4, 8>(sms, d_items, d_order, (uint32_t)n, flags, d_results, t, st);
+      case 6:  return launch_pipeline<2, 24, 19>(sms, d_items, d_order, (uint32_t)n, flags, d_results, t, st);
+      case 7:  return launch_pipeline<1, 32, 16>(sms, d_items, d_order, (uint32_t)n, flags, d_results, t, st);
+      default: return fail("unknown pipeline shape");
+    }
+  }
   switch (lanes) {
     case 1:  return launch_batch<1, 32>(sms, d_items, d_order, (uint32_t)n, flags, d_results, t, st);
     case 2:  return launch_batch<2, 16>(sms, d_items, d_order, (uint32_t)n, flags, d_results, t, st);
@@ -352,8 +391,8 @@ UNZ_EXPORT const char* infl_engine_info(void) {
   static char buf[256];
   int lanes = g_lanes_per_stream.load();
   std::snprintf(buf, sizeof(buf),
-                "defl_b200 %d.%d sm_100a; lanes/stream=%d; smem/stream=%zu B; lit root %d bits, dist root %d bits",
-                DEFL_B200_VERSION_MAJOR, DEFL_B200_VERSION_MINOR, lanes ? lanes : kDefaultLanes,
+                "defl_b200 %d.%d sm_100a; lanes/stream=%d (0 = lane-decoder pipeline); smem/stream=%zu B; lit root %d bits, dist root %d bits",
+                DEFL_B200_VERSION_MAJOR, DEFL_B200_VERSION_MINOR, lanes,
                 sizeof(GroupSmem), defl::kLitRootBits, defl::kDistRootBits);
   return buf;
 }
@@ -364,6 +403,12 @@ UNZ_EXPORT int infl_set_lanes_per_stream(int lanes) {
   if (lanes != 0 && lanes != 1 && lanes != 2 && lanes != 4 && lanes != 8 && lanes != 16 && lanes != 32)
     return fail("lanes per stream must be 0 (default), 1, 2, 4, 8, 16 or 32");
   g_lanes_per_stream.store(lanes);
+  return UNZ_OK;
+}
+
+UNZ_EXPORT int infl_set_pipeline_shape(int shape) {
+  if (shape < 0 || shape > 7) return fail("pipeline shape must be 0..7");
+  g_pipeline_shape.store(shape);
   return UNZ_OK;
 }
 

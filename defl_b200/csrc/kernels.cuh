@@ -2,6 +2,7 @@
 #pragma once
 #include "simt_cuda.cuh"
 #include "inflate_core.cuh"
+#include "pipeline.cuh"
 #include "../../include/defl/infl_batch.h"
 
 namespace defl {
@@ -46,6 +47,44 @@ inflate_batch_kernel(const infl_batch_item_t* __restrict__ items, const uint32_t
     simt::syncwarp(L.gmask);
   }
 }
+
+// K3 (v2): the lane-decoder pipeline of pipeline.cuh.  Persistent CTAs of D decoder warps (SL stream
+// slots each) and K worker warps; decoder lanes pull streams from the global ticket counter.
+template <int D, int SL, int K>
+__global__ void __launch_bounds__((D + K) * 32)
+inflate_pipeline_kernel(const infl_batch_item_t* __restrict__ items, const uint32_t* __restrict__ order,
+                        uint32_t n, int flags, infl_batch_result_t* __restrict__ results,
+                        unsigned int* __restrict__ ticket) {
+  static_assert(D * SL <= 32 * K && D + K <= 32, "every worker polls at most 32 slots; a CTA has at most 32 warps");
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  Slot*       slots = reinterpret_cast<Slot*>(smem_raw);
+  WorkerSmem* wsm   = reinterpret_cast<WorkerSmem*>(smem_raw + sizeof(Slot) * D * SL);
+  uint32_t*   live  = reinterpret_cast<uint32_t*>(wsm + K);
+
+  for (int s = threadIdx.x; s < D * SL; s += blockDim.x) {
+    Slot& sl = slots[s];
+    sl.tail = 0; sl.req = REQ_NONE; sl.req_bit_lo = 0; sl.req_bit_hi = 0; sl.req_reason = 0; sl.stream = 0;
+    sl.head = 0; sl.ack = ACK_NONE; sl.ack_bit_lo = 0; sl.ack_bit_hi = 0; sl.ack_pos = 0; sl.ack_bfinal = 0;
+    sl.wpos = 0; sl.fixed_ready = 0; sl.dst_lo = 0; sl.dst_hi = 0;
+  }
+  if (threadIdx.x == 0) *live = D;
+  __syncthreads();
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (warp < D) {
+    decoder_warp(slots + warp * SL, SL, lane, items, order, n, ticket);
+    __syncwarp();
+    if (lane == 0) {
+      __threadfence_block();
+      atomicSub(live, 1u);
+    }
+  } else {
+    worker_warp(slots, D * SL, warp - D, K, wsm[warp - D], lane, live, items, flags, results);
+  }
+}
+
+template <int D, int SL, int K>
+constexpr size_t pipeline_smem_bytes() { return sizeof(Slot) * D * SL + sizeof(WorkerSmem) * K + 16; }
 
 // K2: descriptor-driven gather of input pieces into contiguous device memory (replaces the
 // host-side join of infl_include, reference src/infl/mem.c:121-155, and the chunk walk of

@@ -36,4 +36,27 @@ DEFL_DEV uint8_t  ld_in8(const uint8_t* p) { return __ldg(p); }
 DEFL_DEV uint4    ld_in128(const uint4* p) { return __ldg(p); }
 DEFL_DEV void     prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
 
+
+// ---- used by the lane-decoder pipeline (pipeline.cuh) -----------------------------------------------
+DEFL_DEV unsigned ballot(unsigned mask, bool p) { return __ballot_sync(mask, p); }
+DEFL_DEV bool     all(unsigned mask, bool p) { return __all_sync(mask, p); }
+DEFL_DEV uint32_t shfl_up(unsigned mask, uint32_t v, unsigned d) { return __shfl_up_sync(mask, v, d); }
+DEFL_DEV int      ffs(uint32_t v) { return __ffs(v); }
+DEFL_DEV uint32_t reduce_or(unsigned mask, uint32_t v) { return __reduce_or_sync(mask, v); }
+DEFL_DEV unsigned lanemask_le() {
+  unsigned m;
+  asm("mov.u32 %0, %%lanemask_le;" : "=r"(m));
+  return m;
+}
+// words shared between warps of a CTA: volatile accesses + block-scope fences
+DEFL_DEV uint32_t vload(const uint32_t* p) { return *reinterpret_cast<const volatile uint32_t*>(p); }
+DEFL_DEV void     vstore(uint32_t* p, uint32_t v) { *reinterpret_cast<volatile uint32_t*>(p) = v; }
+DEFL_DEV void     fence_block() { __threadfence_block(); }
+DEFL_DEV void     backoff(unsigned ns) { __nanosleep(ns); }
+DEFL_DEV uint32_t atomic_add_global(unsigned int* p, unsigned int v) { return atomicAdd(p, v); }
+DEFL_DEV long long ticks() { return clock64(); }
+// decoded output read back as a match source: written earlier by this SM, cached at L2 only so the
+// L1 stays with the compressed input lines the decoder lanes stream through
+DEFL_DEV uint32_t ld_out8(const uint8_t* p) { return __ldcg(p); }
+
 }  // namespace simt

@@ -102,8 +102,11 @@ UNZ_EXPORT const char *infl_last_error(void);       /* thread-local, "" when non
 UNZ_EXPORT const char *infl_engine_info(void);      /* build / kernel configuration string */
 /* number of kernels launched by this library in this process (bench.py's gpu_launches) */
 UNZ_EXPORT uint64_t    infl_kernel_launch_count(void);
-/* tuning knob, mainly for benchmarks: lanes per stream (1,2,4,8,16,32), 0 = default */
+/* tuning knobs, mainly for benchmarks.  lanes per stream: 0 = default engine (the lane-decoder
+   pipeline: one thread decodes, warps copy); 1,2,4,8,16,32 = the group-per-stream kernel.
+   pipeline shape: 0..3 = compiled (decoder warps, slots, worker warps) variants */
 UNZ_EXPORT int         infl_set_lanes_per_stream(int lanes);
+UNZ_EXPORT int         infl_set_pipeline_shape(int shape);
 
 #ifdef __cplusplus
 }

@@ -1,6 +1,8 @@
 // tests/emu/emu_main.cpp -- DEBUG AID, TEST TREE ONLY (see simt_emu.h).
+#define DEFL_WATCHDOG_SPINS (1u << 21)
 #include "simt_emu.h"
 #include "../../defl_b200/csrc/inflate_core.cuh"
+#include "../../defl_b200/csrc/pipeline.cuh"
 
 #include <stdlib.h>
 #include <vector>
@@ -65,4 +67,71 @@ extern "C" int emu_inflate(int G, const uint8_t* src, uint32_t srclen, uint8_t* 
     case 32: return run<32>(src, srclen, dst, cap, flags, out);
   }
   return -99;
+}
+
+// ---- one emulated CTA of the lane-decoder pipeline: (D + K) warps of 32 host threads -----------------
+namespace {
+
+struct PipeCta {
+  int                        D, SL, K;
+  defl::Slot*                slots;
+  defl::WorkerSmem*          wsm;
+  uint32_t                   live;
+  const infl_batch_item_t*   items;
+  uint32_t                   n;
+  int                        flags;
+  infl_batch_result_t*       results;
+  unsigned int               ticket;
+  std::vector<simt::Group>   warps;
+};
+
+struct PipeThread { PipeCta* cta; int warp, lane; };
+
+void* pipe_main(void* arg) {
+  PipeThread* t = static_cast<PipeThread*>(arg);
+  PipeCta*    c = t->cta;
+  simt::t_group = &c->warps[t->warp];
+  simt::t_lane  = t->lane;
+  if (t->warp < c->D) {
+    defl::decoder_warp(c->slots + t->warp * c->SL, c->SL, t->lane, c->items, nullptr, c->n, &c->ticket);
+    simt::syncwarp(0xFFFFFFFFu);
+    if (t->lane == 0) __atomic_fetch_sub(&c->live, 1u, __ATOMIC_SEQ_CST);
+  } else {
+    defl::worker_warp(c->slots, c->D * c->SL, t->warp - c->D, c->K, c->wsm[t->warp - c->D], t->lane, &c->live,
+                      c->items, c->flags, c->results);
+  }
+  return nullptr;
+}
+
+}  // namespace
+
+extern "C" int emu_pipeline(int D, int SL, int K, const infl_batch_item_t* items, uint32_t n, int flags,
+                            infl_batch_result_t* results) {
+  PipeCta c;
+  c.D = D; c.SL = SL; c.K = K; c.items = items; c.n = n; c.flags = flags; c.results = results;
+  c.ticket = 0; c.live = (uint32_t)D;
+  const size_t nslots = (size_t)D * SL;
+  c.slots = static_cast<defl::Slot*>(aligned_alloc(64, ((sizeof(defl::Slot) * nslots + 63) & ~63ul)));
+  c.wsm   = static_cast<defl::WorkerSmem*>(aligned_alloc(64, ((sizeof(defl::WorkerSmem) * K + 63) & ~63ul)));
+  memset(c.slots, 0xA5, sizeof(defl::Slot) * nslots);     // shared memory starts as garbage
+  memset(c.wsm, 0x5A, sizeof(defl::WorkerSmem) * K);
+  for (size_t s = 0; s < nslots; s++) {
+    defl::Slot& sl = c.slots[s];
+    sl.tail = 0; sl.req = 0; sl.req_bit_lo = 0; sl.req_bit_hi = 0; sl.req_reason = 0; sl.stream = 0;
+    sl.head = 0; sl.ack = 0; sl.ack_bit_lo = 0; sl.ack_bit_hi = 0; sl.ack_pos = 0; sl.ack_bfinal = 0;
+    sl.wpos = 0; sl.fixed_ready = 0; sl.dst_lo = 0; sl.dst_hi = 0;
+  }
+  const int nw = D + K;
+  c.warps.resize(nw);
+  for (int w = 0; w < nw; w++) { c.warps[w].G = 32; pthread_barrier_init(&c.warps[w].bar, nullptr, 32); }
+  std::vector<PipeThread> th(nw * 32);
+  std::vector<pthread_t>  tid(nw * 32);
+  for (int i = 0; i < nw * 32; i++) {
+    th[i] = PipeThread{&c, i / 32, i % 32};
+    pthread_create(&tid[i], nullptr, pipe_main, &th[i]);
+  }
+  for (int i = 0; i < nw * 32; i++) pthread_join(tid[i], nullptr);
+  for (int w = 0; w < nw; w++) pthread_barrier_destroy(&c.warps[w].bar);
+  free(c.slots); free(c.wsm);
+  return 0;
 }

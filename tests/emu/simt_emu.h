@@ -7,6 +7,7 @@
 // it is built only by tests/test_emu_logic.py, and the GPU tests never load it.
 #pragma once
 #include <pthread.h>
+#include <sched.h>
 #include <stdint.h>
 #include <string.h>
 
@@ -69,5 +70,41 @@ inline uint32_t dp4a(uint32_t a, uint32_t b, uint32_t c) {
 inline uint32_t ld_in32(const uint32_t* p) { uint32_t v; memcpy(&v, p, 4); return v; }
 inline uint8_t  ld_in8(const uint8_t* p) { return *p; }
 inline void     prefetch_l2(const void*) {}
+
+
+// ---- pipeline primitives: one Group per warp, several warps (thread sets) per emulated CTA -----------
+inline unsigned ballot(unsigned, bool p) {
+  t_group->xchg[t_lane] = p ? 1u : 0u;
+  barrier();
+  unsigned m = 0;
+  for (int i = 0; i < t_group->G; i++) m |= t_group->xchg[i] << i;
+  barrier();
+  return m;
+}
+inline bool all(unsigned mk, bool p) { return ballot(mk, p) == (t_group->G == 32 ? 0xFFFFFFFFu : ((1u << t_group->G) - 1u)); }
+inline uint32_t shfl_up(unsigned, uint32_t v, unsigned d) {
+  t_group->xchg[t_lane] = v;
+  barrier();
+  uint32_t r = (unsigned)t_lane >= d ? t_group->xchg[t_lane - d] : v;
+  barrier();
+  return r;
+}
+inline int ffs(uint32_t v) { return __builtin_ffs((int)v); }
+inline uint32_t reduce_or(unsigned, uint32_t v) {
+  t_group->xchg[t_lane] = v;
+  barrier();
+  uint32_t r = 0;
+  for (int i = 0; i < t_group->G; i++) r |= t_group->xchg[i];
+  barrier();
+  return r;
+}
+inline unsigned lanemask_le() { return t_lane == 31 ? 0xFFFFFFFFu : ((2u << t_lane) - 1u); }
+inline uint32_t vload(const uint32_t* p) { return __atomic_load_n(p, __ATOMIC_ACQUIRE); }
+inline void vstore(uint32_t* p, uint32_t v) { __atomic_store_n(p, v, __ATOMIC_RELEASE); }
+inline void fence_block() { __atomic_thread_fence(__ATOMIC_SEQ_CST); }
+inline void backoff(unsigned) { sched_yield(); }
+inline uint32_t atomic_add_global(unsigned int* p, unsigned int v) { return __atomic_fetch_add(p, v, __ATOMIC_RELAXED); }
+inline long long ticks() { return 0; }
+inline uint32_t ld_out8(const uint8_t* p) { return *(const volatile uint8_t*)p; }
 
 }  // namespace simt

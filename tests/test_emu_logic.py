@@ -65,3 +65,52 @@ def test_mutants_logic(emu):
         G = (1, 2, 4, 8, 16, 32)[it % 6]
         rc, out, o = run(emu, G, d, cap, flags, mis=it % 4)
         assert same(rc, out, o, rc0, out0, r0), (it, G, m, o.info >> 8)
+
+
+# ---- the lane-decoder pipeline (defl_b200/csrc/pipeline.cuh): one emulated CTA ------------------------
+import numpy as np
+
+ITEM = np.dtype([("src", "<u8"), ("srclen", "<u8"), ("dst", "<u8"), ("dstlen", "<u8")])
+RESULT = np.dtype([("code", "<i4"), ("adler", "<u4"), ("outlen", "<u8"), ("inpos", "<u8"),
+                   ("adler_stored", "<u4"), ("info", "<u4")])
+
+
+def run_pipeline(emu, shape, datas, caps, flags):
+    D, SL, K = shape
+    n = len(datas)
+    srcs = [np.frombuffer(bytes(d) + b"\0" * 8, dtype=np.uint8).copy() for d in datas]
+    dsts = [np.zeros(c + 16, dtype=np.uint8) for c in caps]
+    items = np.zeros(n, dtype=ITEM)
+    for i in range(n):
+        items[i] = (srcs[i].ctypes.data + (i % 4 if len(datas[i]) else 0) * 0, len(datas[i]), dsts[i].ctypes.data, caps[i])
+    res = np.full(n, -7, dtype=np.int32).repeat(8).view(RESULT).copy()
+    emu.emu_pipeline(D, SL, K, ctypes.c_void_p(items.ctypes.data), n, flags, ctypes.c_void_p(res.ctypes.data))
+    return res, [bytes(dsts[i][: int(res[i]["outlen"])]) for i in range(n)]
+
+
+def check_pipeline(emu, shape, datas, caps, flags, what):
+    res, outs = run_pipeline(emu, shape, datas, caps, flags)
+    for i, (d, cap) in enumerate(zip(datas, caps)):
+        rc0, out0, r0 = ol.port_inflate(d, cap, flags)
+        g = res[i]
+        assert int(g["code"]) == rc0, (what, i, int(g["info"]) >> 8, rc0)
+        if rc0 == 0:
+            assert outs[i] == out0, (what, i)
+            assert int(g["inpos"]) == r0.inpos and int(g["adler"]) == r0.adler, (what, i)
+            assert (int(g["info"]) & 1) == r0.has_trailer
+
+
+def test_pipeline_corpus_logic(emu, corpus):
+    datas = [e["data"] for e in corpus]
+    caps = [e["cap"] for e in corpus]
+    check_pipeline(emu, (1, 32, 3), datas, caps, 0, "corpus")
+
+
+def test_pipeline_mutants_logic(emu):
+    from test_oracle import _mutants
+    by = {0: ([], []), 1: ([], [])}
+    for d, cap, flags, raw, m in _mutants(31337, 400):
+        by[flags][0].append(d)
+        by[flags][1].append(cap)
+    check_pipeline(emu, (2, 5, 3), by[0][0], by[0][1], 0, "mut0")
+    check_pipeline(emu, (1, 32, 2), by[1][0], by[1][1], 1, "mut1")

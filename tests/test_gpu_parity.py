@@ -13,7 +13,7 @@ import oracle_lib as ol
 
 pytestmark = pytest.mark.gpu
 
-LANES = (1, 2, 4, 8, 16, 32)
+LANES = (0, 1, 2, 4, 8, 16, 32)   # 0 = the default engine (lane-decoder pipeline)
 
 
 def _check_against_port(d, res, outs, datas, caps, flags, what):
@@ -110,7 +110,7 @@ def test_mutants_vs_oracle(gpu_lib):
         by_flag[flags][0].append(data)
         by_flag[flags][1].append(cap)
     try:
-        for lanes in (1, 4, 8, 32):
+        for lanes in (0, 1, 8, 32):
             d.set_lanes_per_stream(lanes)
             for flags, (datas, caps) in by_flag.items():
                 res, outs = d.infl_buf_batch(datas, caps, flags)
@@ -284,3 +284,29 @@ def test_gather_kernel(gpu_lib):
     torch.cuda.synchronize()
     want = np.concatenate([blob[int(o):int(o) + int(n)] for o, n in zip(srcoff, lens)])
     assert np.array_equal(out.cpu().numpy()[:total], want)
+
+
+def test_pipeline_shapes(gpu_lib):
+    """Every compiled (decoder warps, slots, worker warps) variant of the default engine, mixed payloads."""
+    from defl_b200 import synth
+    d = gpu_lib
+    specs = []
+    for i in range(160):
+        kind = ("text", "log", "png", "rand", "zero")[i % 5]
+        size = (1000, 65536, 200000, 33000, 5)[(i // 5) % 5]
+        level, strat = ((6, zlib.Z_DEFAULT_STRATEGY), (1, zlib.Z_DEFAULT_STRATEGY), (9, zlib.Z_DEFAULT_STRATEGY),
+                        (6, zlib.Z_FIXED), (0, zlib.Z_DEFAULT_STRATEGY))[(i // 25) % 5]
+        specs.append((kind, size, 500 + i, level, strat))
+    streams = synth.make_streams(specs)
+    zs = [z for _, z in streams]
+    caps = [len(r) for r, _ in streams]
+    try:
+        for shape in range(8):
+            d.set_pipeline_shape(shape)
+            res, outs = d.infl_buf_batch(zs, caps, d.INFL_ZLIB | d.INFL_BATCH_VERIFY_ADLER)
+            for i, (raw, z) in enumerate(streams):
+                assert int(res[i]["code"]) == 0, (shape, i, int(res[i]["info"]) >> 8)
+                assert bytes(outs[i]) == raw, (shape, i)
+                assert int(res[i]["adler"]) == (zlib.adler32(raw) & 0xFFFFFFFF)
+    finally:
+        d.set_pipeline_shape(0)
