@@ -43,6 +43,7 @@ def parse():
     ap.add_argument("--unique", type=int, default=8192, help="distinct streams generated on the host")
     ap.add_argument("--lanes", type=int, default=0, help="lanes per stream (0 = engine default)")
     ap.add_argument("--shape", type=int, default=-1, help="pipeline shape (engine default when < 0)")
+    ap.add_argument("--engine", type=int, default=0, help="3 = warp per stream (default), 2 = lane-decoder pipeline")
     ap.add_argument("--e2e-steps", type=int, default=2)
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
@@ -224,6 +225,8 @@ def main():
         d.set_lanes_per_stream(args.lanes)
     if args.shape >= 0:
         d.set_pipeline_shape(args.shape)
+    if args.engine:
+        d.set_engine(args.engine)
 
     n = args.streams
     unique = min(args.unique, n)
@@ -296,7 +299,8 @@ def main():
     kern_ms = float(np.mean(step_ms))
     achieved = (in_bytes + out_bytes) / (kern_ms / 1e3) / 1e9
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                "traffic": None, "peak_source": peak_src, "kernel": "inflate_pipeline_kernel" if not args.lanes else "inflate_batch_kernel",
+                "traffic": None, "peak_source": peak_src, "kernel": "inflate_batch_kernel" if args.lanes else
+                ("inflate_pipeline_kernel" if args.engine == 2 else "inflate_warp_kernel"),
                 "algorithmic_bytes_per_launch": in_bytes + out_bytes,
                 "kernel_ms": kern_ms}
     prof = os.path.join(ROOT, "profiles", "traffic.json")

@@ -12,5 +12,6 @@ from .api import (  # noqa: F401
     INFL_BATCH_VERIFY_ADLER, INFL_BATCH_DEVICE_PTRS, INFL_BATCH_ALL_GPUS, INFL_BATCH_NO_SPLIT,
     ITEM_DTYPE, RESULT_DTYPE,
     lib, infl_buf, infl_buf_batch, infl_buf_batch_iov, InflStream, DeviceBatch,
-    last_error, engine_info, kernel_launch_count, set_lanes_per_stream, set_pipeline_shape, EXPORTED_SYMBOLS,
+    last_error, engine_info, kernel_launch_count, set_lanes_per_stream, set_pipeline_shape, set_engine,
+    EXPORTED_SYMBOLS,
 )

@@ -38,7 +38,7 @@ EXPORTED_SYMBOLS = [
     "infl_buf_batch", "infl_buf_batch_iov", "infl_batch_workspace_size", "infl_batch_decode_device",
     "infl_gather_device",
     "infl_device_count", "infl_last_error", "infl_engine_info",
-    "infl_kernel_launch_count", "infl_set_lanes_per_stream", "infl_set_pipeline_shape",
+    "infl_kernel_launch_count", "infl_set_lanes_per_stream", "infl_set_pipeline_shape", "infl_set_engine",
 ]
 
 _lib = None
@@ -97,6 +97,8 @@ def lib():
     L.infl_set_lanes_per_stream.argtypes = [i32]
     L.infl_set_pipeline_shape.restype = i32
     L.infl_set_pipeline_shape.argtypes = [i32]
+    L.infl_set_engine.restype = i32
+    L.infl_set_engine.argtypes = [i32]
     _lib = L
     return L
 
@@ -120,6 +122,12 @@ def set_lanes_per_stream(lanes):
 
 def set_pipeline_shape(shape):
     if lib().infl_set_pipeline_shape(int(shape)) != UNZ_OK:
+        raise ValueError(last_error())
+
+
+def set_engine(engine):
+    """3 = warp per stream (default), 2 = lane-decoder pipeline, 1 = group per stream."""
+    if lib().infl_set_engine(int(engine)) != UNZ_OK:
         raise ValueError(last_error())
 
 

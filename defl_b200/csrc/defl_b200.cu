@@ -171,13 +171,60 @@ int launch_pipeline(int sms, const infl_batch_item_t* d_items, const uint32_t* d
   return UNZ_OK;
 }
 
+// ---- v3 (default engine): one warp per stream --------------------------------------------------------------
+constexpr int    kWarpsPerCta = 4;
+constexpr size_t kWsHeader    = 256;     // ticket counter and friends live in front of the token scratch
+
+int warp_kernel_grid(int sms, int* grid_out) {
+  auto         kern = defl::inflate_warp_kernel<kWarpsPerCta>;
+  const size_t smem = sizeof(defl::WarpSmem) * kWarpsPerCta;
+  static int   ctas_per_sm[kMaxDevices] = {0};
+  int          dev = 0;
+  cudaGetDevice(&dev);
+  if (!ctas_per_sm[dev]) {
+    CU_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem),
+           "cudaFuncSetAttribute(smem)");
+    int occ = 0;
+    CU_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, kWarpsPerCta * 32, smem), "occupancy query");
+    if (occ < 1) return fail("inflate warp kernel does not fit on an SM");
+    ctas_per_sm[dev] = occ;
+  }
+  *grid_out = sms * ctas_per_sm[dev];
+  return UNZ_OK;
+}
+
+size_t warp_kernel_workspace(int sms) {
+  int grid = 0;
+  if (warp_kernel_grid(sms, &grid) != UNZ_OK) return 0;
+  return kWsHeader + (size_t)grid * kWarpsPerCta * defl::kWarpScratchBytes;
+}
+
+int launch_warp(int sms, const infl_batch_item_t* d_items, const uint32_t* d_order, uint32_t n, int flags,
+                infl_batch_result_t* d_results, void* d_ws, cudaStream_t st) {
+  int grid = 0;
+  if (warp_kernel_grid(sms, &grid) != UNZ_OK) return UNZ_ERR;
+  grid = (int)std::max<uint64_t>(1, std::min<uint64_t>((uint64_t)grid, (n + kWarpsPerCta - 1) / kWarpsPerCta));
+  auto* ticket  = static_cast<unsigned int*>(d_ws);
+  auto* scratch = static_cast<unsigned char*>(d_ws) + kWsHeader;
+  CU_TRY(cudaMemsetAsync(ticket, 0, sizeof(unsigned int), st), "cudaMemsetAsync(ticket)");
+  defl::inflate_warp_kernel<kWarpsPerCta><<<(unsigned)grid, kWarpsPerCta * 32, sizeof(defl::WarpSmem) * kWarpsPerCta, st>>>(
+      d_items, d_order, n, flags, d_results, ticket, scratch);
+  CU_TRY(cudaGetLastError(), "inflate_warp_kernel launch");
+  g_launches.fetch_add(1, std::memory_order_relaxed);
+  return UNZ_OK;
+}
+
+std::atomic<int> g_engine{3};   // 3 = warp per stream (default), 2 = lane-decoder pipeline, 1 = group per stream
+
 int launch_batch_any(int sms, const infl_batch_item_t* d_items, const uint32_t* d_order, size_t n, int flags,
                      infl_batch_result_t* d_results, void* d_ws, cudaStream_t st) {
   if (n == 0) return UNZ_OK;
   if (n > 0xFFFFFFFFull) return fail("batch too large (n must fit 32 bits)");
   int  lanes = g_lanes_per_stream.load();
   auto t = static_cast<unsigned int*>(d_ws);
-  if (!lanes) {   // default: the lane-decoder pipeline (v2)
+  if (!lanes && g_engine.load() == 3)
+    return launch_warp(sms, d_items, d_order, (uint32_t)n, flags, d_results, d_ws, st);
+  if (!lanes) {   // the lane-decoder pipeline (v2)
     switch (g_pipeline_shape.load()) {
       case 0:  return launch_pipeline<2, 24, 14>(sms, d_items, d_order, (uint32_t)n, flags, d_results, t, st);
       case 1:  return launch_pipeline<2, 24, 8>(sms, d_items, d_order, (uint32_t)n, flags, d_results, t, st);
@@ -256,7 +303,7 @@ int run_host_batch_on_device(const infl_batch_item_t* items, size_t n, int flags
 
   if (E->d_in.reserve(in_total + 64) || E->d_out.reserve(out_total + 64) ||
       E->d_items.reserve(n * sizeof(infl_batch_item_t)) || E->d_results.reserve(n * sizeof(infl_batch_result_t)) ||
-      E->d_order.reserve(n * sizeof(uint32_t)) || E->d_ws.reserve(256) ||
+      E->d_order.reserve(n * sizeof(uint32_t)) || E->d_ws.reserve(warp_kernel_workspace(E->sms)) ||
       E->h_items.reserve(n * sizeof(infl_batch_item_t)) || E->h_results.reserve(n * sizeof(infl_batch_result_t)) ||
       E->h_order.reserve(n * sizeof(uint32_t)))
     return UNZ_ERR;
@@ -312,7 +359,7 @@ int run_device_batch(const infl_batch_item_t* items, size_t n, int flags, infl_b
   std::lock_guard<std::mutex> guard(E->mu);
   cudaStream_t st = E->stream;
   if (E->d_items.reserve(n * sizeof(infl_batch_item_t)) || E->d_results.reserve(n * sizeof(infl_batch_result_t)) ||
-      E->d_order.reserve(n * sizeof(uint32_t)) || E->d_ws.reserve(256) ||
+      E->d_order.reserve(n * sizeof(uint32_t)) || E->d_ws.reserve(warp_kernel_workspace(E->sms)) ||
       E->h_order.reserve(n * sizeof(uint32_t)))
     return UNZ_ERR;
   auto* ho = static_cast<uint32_t*>(E->h_order.p);
@@ -390,10 +437,14 @@ UNZ_EXPORT const char* infl_last_error(void) { return g_last_error.c_str(); }
 UNZ_EXPORT const char* infl_engine_info(void) {
   static char buf[256];
   int lanes = g_lanes_per_stream.load();
+  const int engine = lanes ? 1 : g_engine.load();
   std::snprintf(buf, sizeof(buf),
-                "defl_b200 %d.%d sm_100a; lanes/stream=%d (0 = lane-decoder pipeline); smem/stream=%zu B; lit root %d bits, dist root %d bits",
-                DEFL_B200_VERSION_MAJOR, DEFL_B200_VERSION_MINOR, lanes,
-                sizeof(GroupSmem), defl::kLitRootBits, defl::kDistRootBits);
+                "defl_b200 %d.%d sm_100a; engine=%d (%s); lanes/stream=%d; smem/warp=%zu B; window<=32x%u bits; "
+                "lit root %d bits, dist root %d bits",
+                DEFL_B200_VERSION_MAJOR, DEFL_B200_VERSION_MINOR, engine,
+                engine == 3 ? "warp per stream, speculative sub-sequences" : engine == 2 ? "lane-decoder pipeline"
+                                                                                          : "group per stream",
+                lanes, sizeof(defl::WarpSmem), defl::kSubMax, defl::kLitRootBits, defl::kDistRootBits);
   return buf;
 }
 
@@ -413,8 +464,16 @@ UNZ_EXPORT int infl_set_pipeline_shape(int shape) {
 }
 
 UNZ_EXPORT size_t infl_batch_workspace_size(size_t n) {
-  (void)n;
-  return 256;
+  (void)n;   // the scratch is per resident warp, not per stream
+  Engine* E = nullptr;
+  if (engine_for_current_device(&E) != UNZ_OK) return 0;
+  return warp_kernel_workspace(E->sms);
+}
+
+UNZ_EXPORT int infl_set_engine(int engine) {
+  if (engine < 1 || engine > 3) return fail("engine must be 1 (group per stream), 2 (lane-decoder pipeline) or 3 (warp per stream)");
+  g_engine.store(engine);
+  return UNZ_OK;
 }
 
 UNZ_EXPORT int infl_batch_decode_device(const infl_batch_item_t* d_items, const uint32_t* d_order, size_t n,
@@ -549,7 +608,7 @@ UNZ_EXPORT int infl_buf_batch_iov(const infl_batch_iov_item_t* items, size_t n, 
       flat[i].dstlen = items[i].dstlen;
     }
     if (E->d_items.reserve(n * sizeof(infl_batch_item_t)) || E->d_results.reserve(n * sizeof(infl_batch_result_t)) ||
-        E->d_order.reserve(n * sizeof(uint32_t)) || E->d_ws.reserve(256) || E->h_order.reserve(n * sizeof(uint32_t)))
+        E->d_order.reserve(n * sizeof(uint32_t)) || E->d_ws.reserve(warp_kernel_workspace(E->sms)) || E->h_order.reserve(n * sizeof(uint32_t)))
       return UNZ_ERR;
     auto* ho = static_cast<uint32_t*>(E->h_order.p);
     size_order(flat.data(), n, ho);

@@ -33,6 +33,7 @@ constexpr int kDistRootBits = 8;
 constexpr int kDistRoot     = 1 << kDistRootBits;
 constexpr int kDistTab      = 512;   // root + worst-case sub-tables (<= 256)
 constexpr uint32_t kAdlerMod = 65521u;
+constexpr uint32_t kFull     = 0xFFFFFFFFu;   // every lane of a warp
 
 // failure reasons (diagnostics only; every one of them is UNZ_ERR at the API)
 enum Reason : uint32_t {

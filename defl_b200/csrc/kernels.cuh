@@ -3,6 +3,7 @@
 #include "simt_cuda.cuh"
 #include "inflate_core.cuh"
 #include "pipeline.cuh"
+#include "warp_decode.cuh"
 #include "../../include/defl/infl_batch.h"
 
 namespace defl {
@@ -85,6 +86,43 @@ inflate_pipeline_kernel(const infl_batch_item_t* __restrict__ items, const uint3
 
 template <int D, int SL, int K>
 constexpr size_t pipeline_smem_bytes() { return sizeof(Slot) * D * SL + sizeof(WorkerSmem) * K + 16; }
+
+// K3 (v3, default): one warp per stream, the 32 lanes decode 32 sub-sequences of the current block at
+// once (warp_decode.cuh).  Persistent CTAs of WARPS warps; each warp owns a slice of the global token
+// scratch and pulls streams from the ticket counter.
+template <int WARPS>
+__global__ void __launch_bounds__(WARPS * 32, 32 / WARPS)
+inflate_warp_kernel(const infl_batch_item_t* __restrict__ items, const uint32_t* __restrict__ order,
+                    uint32_t n, int flags, infl_batch_result_t* __restrict__ results,
+                    unsigned int* __restrict__ ticket, unsigned char* __restrict__ scratch) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  WarpSmem&         sm = reinterpret_cast<WarpSmem*>(smem_raw)[warp];
+  const WarpScratch sc = scratch_of(scratch + ((size_t)blockIdx.x * WARPS + warp) * kWarpScratchBytes);
+
+  for (;;) {
+    uint32_t k = 0;
+    if (lane == 0) k = atomicAdd(ticket, 1u);
+    k = simt::shfl(kFull, k, 0);
+    if (k >= n) break;
+    const uint32_t idx = order ? order[k] : k;
+    const infl_batch_item_t it = items[idx];
+    StreamOut o;
+    if (it.srclen > 0xFFFFFFFFull || it.dstlen > 0xFFFFFFFFull) {
+      o.code = -1; o.adler = 1; o.outlen = 0; o.inpos = 0; o.adler_stored = 0; o.info = R_TRUNCATED << 8;
+    } else {
+      inflate_stream_warp(sm, sc, lane, static_cast<const uint8_t*>(it.src), (uint32_t)it.srclen,
+                          static_cast<uint8_t*>(it.dst), (uint32_t)it.dstlen, flags, o);
+    }
+    if (lane == 0) {
+      infl_batch_result_t r;
+      r.code = o.code; r.adler = o.adler; r.outlen = o.outlen; r.inpos = o.inpos;
+      r.adler_stored = o.adler_stored; r.info = o.info;
+      results[idx] = r;
+    }
+    simt::syncwarp(kFull);
+  }
+}
 
 // K2: descriptor-driven gather of input pieces into contiguous device memory (replaces the
 // host-side join of infl_include, reference src/infl/mem.c:121-155, and the chunk walk of

@@ -29,7 +29,6 @@ constexpr int      kStage    = 512;          // output bytes resolved per batch
 constexpr uint32_t kTokMatch = 0x80000000u;  // [8:0] length, [23:9] distance - 1
 constexpr uint32_t kTokDep   = 0x40000000u;  // worker-side mark: match reads bytes of its own batch
                                              // literal token: [26:24] count (1..3), [23:0] bytes
-constexpr uint32_t kFull     = 0xFFFFFFFFu;
 #ifndef DEFL_WATCHDOG_SPINS
 #define DEFL_WATCHDOG_SPINS (1u << 24)
 #endif

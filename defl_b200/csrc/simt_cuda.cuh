@@ -59,4 +59,10 @@ DEFL_DEV long long ticks() { return clock64(); }
 // L1 stays with the compressed input lines the decoder lanes stream through
 DEFL_DEV uint32_t ld_out8(const uint8_t* p) { return __ldcg(p); }
 
+// ---- used by the warp-per-stream decoder (warp_decode.cuh) ------------------------------------------
+DEFL_DEV bool     any(unsigned mask, bool p) { return __any_sync(mask, p); }
+DEFL_DEV int      clz(uint32_t v) { return __clz((int)v); }
+// tokens written to the global scratch by one lane and read back by the whole warp: L2 only
+DEFL_DEV uint32_t ld_tok(const uint32_t* p) { return __ldcg(p); }
+
 }  // namespace simt

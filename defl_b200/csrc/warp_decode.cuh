@@ -1,0 +1,455 @@
+// warp_decode.cuh -- batch inflate v3: ONE WARP PER STREAM, 32 lanes decode 32 sub-sequences of the
+// current Huffman block at once.
+//
+// Why (profiles/r01_v2_*): with one decoding *thread* per stream (v2) an SM holds ~48 streams -- the
+// decode tables of a stream take 4 KiB of shared memory -- and every symbol is a ~150-cycle dependent
+// chain, so the SM idles on latency.  Here the 32 lanes of a warp share ONE table set and each decodes
+// its own slice of the block's bits, so 32x more symbol chains are in flight per table.
+//
+// How (replaces the reference's serial loop infl_ft_block, infl.c:717-901, result-identical):
+//   1. window  : the next 32*S bits of the block are cut into 32 sub-sequences of S bits.
+//   2. spec    : lane i decodes from bit i*S *assuming* a symbol starts there, writes tokens to its own
+//                segment of a global scratch and notes, every 128 bits, where a token started
+//                ("checkpoints").  Lane 0 starts at a known boundary.
+//   3. fix-up  : Huffman codes self-synchronise: lane i re-decodes from the position where lane i-1
+//                really ended until it meets its own speculative trajectory at a checkpoint; from there
+//                on the speculative tokens are the true ones.  Repeated until no lane's end moves
+//                (a fixed point; at most 31 rounds, in practice one).
+//   4. resolve : the warp walks the tokens in stream order, 32 at a time, and produces the bytes
+//                one byte per lane (coalesced), which is also where distance / capacity are checked.
+// Stored blocks, block headers, table construction and Adler-32 are the warp-cooperative pieces of
+// inflate_core.cuh.
+#pragma once
+#include "inflate_core.cuh"
+#include "../../include/defl/infl_batch.h"
+
+namespace defl {
+
+constexpr uint32_t kSubMax    = 8192;                 // bits per lane per window, at most
+constexpr uint32_t kSubMin    = 512;
+constexpr uint32_t kCpBits    = 128;                  // checkpoint spacing
+constexpr uint32_t kCpPerLane = kSubMax / kCpBits;
+constexpr uint32_t kSpecCap   = 1024;                 // tokens per lane per window (speculative pass)
+constexpr uint32_t kFixCap    = 256;                  // tokens per lane per window (fix-up pass)
+constexpr size_t   kWarpScratchBytes = 32u * (kSpecCap + kFixCap) * 4u + 32u * kCpPerLane * 2u;
+static_assert(kWarpScratchBytes % 16 == 0, "scratch slices stay 16-byte aligned");
+
+constexpr int      kStageV3   = 512;                  // output bytes resolved per token batch
+constexpr uint32_t kTokIsMatch = 0x80000000u;         // [8:0] length, [23:9] distance - 1
+constexpr uint32_t kTokIsDep   = 0x40000000u;         // resolver-side mark
+                                                      // literal token: [26:24] count (1..2), [23:0] bytes
+
+// lane status after a pass: 0 = ran to the end of its sub-sequence; else why it stopped
+enum : uint32_t { LS_OK = 0, LS_EOB = 1, LS_FULL = 2, LS_FAIL = 3, LS_NONE = 4 };   // LS_FAIL | reason << 8
+
+struct WarpSmem {
+  uint16_t lit[kLitTab];
+  uint16_t dist[kDistTab];
+  union {
+    BuildScratch s;              // while a block header is parsed
+    uint8_t      stage[kStageV3];  // while tokens are resolved
+  };
+};
+static_assert(sizeof(WarpSmem) % 16 == 0, "WarpSmem alignment");
+
+// ---- per-lane bit reader: a 96-bit window in registers, positions relative to the window base word ----
+struct SubReader {
+  const uint32_t* w;
+  uint32_t        wend, widx;
+  uint32_t        w0, w1, w2;
+  uint32_t        bo;
+
+  DEFL_DEV uint32_t ld(uint32_t i) const { return i < wend ? simt::ld_in32(w + i) : 0u; }
+  DEFL_DEV void seek(uint32_t word, uint32_t bit) {
+    widx = word + (bit >> 5);
+    bo   = bit & 31u;
+    w0 = ld(widx); w1 = ld(widx + 1); w2 = ld(widx + 2);
+  }
+  DEFL_DEV void consume(uint32_t n) {     // n <= 48, bo < 32 on entry
+    bo += n;
+    if (bo >= 32u) { w0 = w1; w1 = w2; widx++; bo -= 32u; w2 = ld(widx + 2); }
+    if (bo >= 32u) { w0 = w1; w1 = w2; widx++; bo -= 32u; w2 = ld(widx + 2); }
+  }
+};
+
+DEFL_DEV uint32_t fail_stat(uint32_t reason) { return LS_FAIL | (reason << 8); }
+
+// Decode the token that starts at the reader's position.  `avail` = input bits from here to the end
+// of the stream; a symbol whose bits are not all there fails (infl.c:741-745,806-810).
+// Returns LS_OK with (tok, used), LS_EOB with used = the code's bits, or LS_FAIL | reason << 8.
+DEFL_DEV uint32_t decode_token(const uint16_t* lit, const uint16_t* dist, const SubReader& br, uint32_t avail,
+                               bool pack, uint32_t& tok, uint32_t& used) {
+  const uint32_t v0 = simt::funnel_r(br.w0, br.w1, br.bo);
+  const uint32_t v1 = simt::funnel_r(br.w1, br.w2, br.bo);
+  uint32_t       e  = lit[v0 & (kLitRoot - 1)];
+  if ((e & (kLitIsLen | kLitKind)) == kLitSub)
+    e = lit[kLitRoot + (e & 0x1FFu) + ((v0 >> kLitRootBits) & ((1u << ((e >> 11) & 15u)) - 1u))];
+  const uint32_t cl = (e >> 11) & 15u;
+  used = cl;
+  tok = 0;
+  if (e == 0u) return fail_stat(avail < 15u ? R_TRUNCATED : R_SYMBOL);
+  if ((e & (kLitIsLen | kLitKind)) == kLitEob) return cl > avail ? fail_stat(R_TRUNCATED) : (uint32_t)LS_EOB;
+
+  const bool     is_len = (e & kLitIsLen) != 0u;
+  const uint32_t xb   = (e >> 8) & 7u;                        // 0 for a literal
+  const uint32_t val  = (e & 255u) + simt::bfe(v0, cl, xb);   // byte, or length - 3
+  const uint32_t use1 = cl + xb;                              // <= 20
+  const uint32_t v2   = simt::funnel_r(v0, v1, use1);         // the 32 bits after this symbol
+  uint32_t       use2;
+  if (is_len) {
+    uint32_t x = dist[v2 & (kDistRoot - 1)];
+    if (x & kDistSub)
+      x = dist[kDistRoot + (x & 0x1FFu) + ((v2 >> kDistRootBits) & ((1u << ((x >> 11) & 15u)) - 1u))];
+    if (x == 0u) return fail_stat((use1 > avail || avail - use1 < 15u) ? R_TRUNCATED : R_DISTANCE);
+    const uint32_t dcl = (x >> 11) & 15u, dxb = (x >> 7) & 15u;
+    const uint32_t d1  = ((x & 3u) << dxb) + simt::bfe(v2, dcl, dxb);   // distance - 1
+    use2 = dcl + dxb;
+    tok  = kTokIsMatch | (d1 << 9) | (val + 3u);
+  } else {
+    const uint32_t x   = lit[v2 & (kLitRoot - 1)];
+    const uint32_t xcl = (x >> 11) & 15u;
+    const bool two = pack && (x & (kLitIsLen | kLitKind)) == 0u && x != 0u && use1 + xcl <= avail;
+    use2 = two ? xcl : 0u;
+    tok  = two ? ((2u << 24) | ((x & 255u) << 8) | val) : ((1u << 24) | val);
+  }
+  used = use1 + use2;
+  if (used > avail) return fail_stat(R_TRUNCATED);
+  return LS_OK;
+}
+
+// what one lane knows about its sub-sequence after the passes
+struct LaneTraj {
+  uint32_t land;   // window-relative bit where its trajectory ended (first token start >= its limit, or the stop)
+  uint32_t stat;   // LS_*
+  uint32_t n;      // speculative tokens written
+  uint32_t m;      // first speculative token that belongs to the true trajectory
+  uint32_t nf;     // fix-up tokens in front of them
+  uint32_t T;      // where its true trajectory starts
+  uint32_t ncp;    // checkpoints its speculative pass recorded
+  uint32_t s_land, s_stat, s_n;   // how the speculative trajectory ended (valid again after any later merge)
+};
+
+// speculative pass: decode from `start` (window-relative bits) to `limit`
+DEFL_DEV void lane_spec(const uint16_t* lit, const uint16_t* dist, const uint32_t* words, uint32_t wend,
+                        uint32_t bw, uint32_t start, uint32_t limit, uint32_t endr, uint32_t* seg,
+                        uint16_t* cps, LaneTraj& tj) {
+  SubReader br;
+  br.w = words; br.wend = wend;
+  br.seek(bw, start);
+  uint32_t r = start, t = 0, k = 0, next_cp = start, stat = LS_OK;
+  for (;;) {
+    if (r >= limit) break;
+    if (t == kSpecCap) { stat = LS_FULL; break; }
+    if (r >= next_cp) {
+      cps[k] = (uint16_t)((r - next_cp) | (t << 6));
+      k++;
+      next_cp += kCpBits;
+    }
+    uint32_t tok, used;
+    const uint32_t s = decode_token(lit, dist, br, endr > r ? endr - r : 0u, true, tok, used);
+    if (s != LS_OK) {
+      stat = s;
+      if (s == LS_EOB) r += used;
+      break;
+    }
+    seg[t++] = tok;
+    r += used;
+    br.consume(used);
+  }
+  tj.land = r; tj.stat = stat; tj.n = t; tj.m = 0; tj.nf = 0; tj.T = start; tj.ncp = k;
+  tj.s_land = r; tj.s_stat = stat; tj.s_n = t;
+}
+
+// fix-up pass: decode from the true start `T` until the speculative trajectory is met at a checkpoint
+DEFL_DEV void lane_redo(const uint16_t* lit, const uint16_t* dist, const uint32_t* words, uint32_t wend,
+                        uint32_t bw, uint32_t start, uint32_t limit, uint32_t endr, uint32_t* fix,
+                        const uint16_t* cps, uint32_t T, LaneTraj& tj) {
+  SubReader br;
+  br.w = words; br.wend = wend;
+  br.seek(bw, T);
+  uint32_t r = T, f = 0;
+  uint32_t k = (T - start + kCpBits - 1u) / kCpBits;
+  const uint32_t ncp = tj.ncp;
+  uint32_t c = k < ncp ? cps[k] : 0u;
+  uint32_t target = k < ncp ? start + k * kCpBits + (c & 63u) : 0xFFFFFFFFu;
+  tj.T = T;
+  for (;;) {
+    while (r > target) {
+      k++;
+      c = k < ncp ? cps[k] : 0u;
+      target = k < ncp ? start + k * kCpBits + (c & 63u) : 0xFFFFFFFFu;
+    }
+    if (r == target) {            // met the speculative trajectory: its tokens from c >> 6 on are true
+      tj.m = c >> 6; tj.nf = f;
+      tj.land = tj.s_land; tj.stat = tj.s_stat; tj.n = tj.s_n;
+      return;
+    }
+    uint32_t stat = LS_OK;
+    if (r >= limit) {
+      // ran through the whole sub-sequence without meeting it
+    } else if (f == kFixCap) {
+      stat = LS_FULL;
+    } else {
+      uint32_t tok, used;
+      const uint32_t s = decode_token(lit, dist, br, endr > r ? endr - r : 0u, false, tok, used);
+      if (s == LS_OK) {
+        fix[f++] = tok;
+        r += used;
+        br.consume(used);
+        continue;
+      }
+      stat = s;
+      if (s == LS_EOB) r += used;
+    }
+    tj.land = r; tj.stat = stat; tj.n = 0; tj.m = 0; tj.nf = f;
+    return;
+  }
+}
+
+// ---- resolve: tokens -> bytes, in stream order ------------------------------------------------------------
+// toks[0..count) are consecutive tokens of the stream; the bytes they produce start at dst[P].
+// Checks what needs the absolute position (infl.c:816-821): distance > produced so far, output full.
+// Returns a Reason; P advances over everything produced before a failing token.
+DEFL_DEV uint32_t resolve_tokens(uint8_t* stage, int lane, const uint32_t* toks, uint32_t count, uint8_t* dst0,
+                                 uint32_t cap, uint32_t& P) {
+  const unsigned le = simt::lanemask_le();
+  uint32_t h = 0;
+#pragma unroll 1
+  while (h < count) {
+    uint32_t n = count - h < 32u ? count - h : 32u;
+    uint32_t tok = (uint32_t)lane < n ? simt::ld_tok(toks + h + lane) : 0u;
+    uint32_t olen = (tok >> 31) ? (tok & 511u) : ((tok >> 24) & 7u);
+
+    uint32_t inc = olen;                                   // inclusive prefix sum of output lengths
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const uint32_t t = simt::shfl_up(kFull, inc, d);
+      if (lane >= d) inc += t;
+    }
+    const uint32_t o = inc - olen;                         // this token's first byte inside the batch
+    const uint32_t d1 = (tok >> 9) & 0x7FFFu;              // distance - 1
+    const bool bad_dist = (tok >> 31) && d1 >= P + o;
+    const bool bad_full = olen != 0u && inc > cap - P;
+    const bool nofit    = inc > (uint32_t)kStageV3;
+    // all three are monotone or first-hit: keep the tokens before the first stop
+    const unsigned stop = simt::ballot(kFull, bad_dist || bad_full || nofit || (uint32_t)lane >= n);
+    const uint32_t keep = stop ? (uint32_t)simt::ffs(stop) - 1u : 32u;
+    if (keep == 0u) {
+      // token 0 of the batch fails (one token always fits the stage: <= 258 bytes)
+      const uint32_t bd = simt::shfl(kFull, (uint32_t)bad_dist, 0);
+      return bd ? R_DISTANCE : R_OUTPUT_FULL;
+    }
+    n = keep;
+    if ((uint32_t)lane >= n) { tok = 0u; olen = 0u; }
+    const uint32_t B = simt::shfl(kFull, inc, (int)n - 1);
+    uint8_t*       dst = dst0 + P;
+
+    const bool dep = (tok >> 31) && (d1 + 1u < o + olen);
+    if (dep) tok |= kTokIsDep;
+
+    const bool     valid = olen != 0u;
+    const uint32_t ks = o >> 5, kb = 1u << (o & 31u);
+    simt::syncwarp(kFull);
+#pragma unroll 1
+    for (uint32_t base = 0; base < B; base += 128u) {
+      uint32_t val[4];
+      bool     have[4];
+#pragma unroll
+      for (int u = 0; u < 4; u++) {
+        const uint32_t rb = base + 32u * (uint32_t)u;
+        have[u] = false;
+        val[u] = 0;
+        if (rb < B) {                                      // uniform
+          const uint32_t k = rb >> 5;
+          const uint32_t before = (uint32_t)simt::popc(simt::ballot(kFull, valid && ks < k));
+          const uint32_t starts = simt::reduce_or(kFull, (valid && ks == k) ? kb : 0u);
+          const int      i  = (int)((before + (uint32_t)simt::popc(starts & le) - 1u) & 31u);
+          const uint32_t t  = simt::shfl(kFull, tok, i);
+          const uint32_t oi = simt::shfl(kFull, o, i);
+          const uint32_t j  = rb + (uint32_t)lane;
+          if (j < B) {
+            if (!(t >> 31)) {
+              val[u] = (t >> (8u * (j - oi))) & 255u;
+              have[u] = true;
+            } else if (!(t & kTokIsDep)) {
+              val[u] = simt::ld_out8(dst + j - (((t >> 9) & 0x7FFFu) + 1u));
+              have[u] = true;
+            }
+          }
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < 4; u++) {
+        const uint32_t j = base + 32u * (uint32_t)u + (uint32_t)lane;
+        if (have[u]) {
+          stage[j] = (uint8_t)val[u];
+          dst[j] = (uint8_t)val[u];
+        }
+      }
+    }
+
+    // matches that read bytes of this very batch: in token order, each by the whole warp
+    unsigned depmask = simt::ballot(kFull, dep);
+#pragma unroll 1
+    while (depmask) {
+      const int i = simt::ffs(depmask) - 1;
+      depmask &= depmask - 1u;
+      const uint32_t t  = simt::shfl(kFull, tok, i);
+      const uint32_t oi = simt::shfl(kFull, o, i);
+      const uint32_t len = t & 511u, dist = ((t >> 9) & 0x7FFFu) + 1u;
+      simt::syncwarp(kFull);
+      for (uint32_t r = (uint32_t)lane; r < len; r += 32u) {
+        const uint32_t sr = dist < len ? r % dist : r;     // a period shorter than the match repeats
+        const int32_t  so = (int32_t)oi - (int32_t)dist + (int32_t)sr;
+        const uint8_t  v  = so < 0 ? (uint8_t)simt::ld_out8(dst + so) : stage[so];
+        stage[oi + r] = v;
+        dst[oi + r] = v;
+      }
+    }
+    simt::syncwarp(kFull);
+    P += B;
+    h += n;
+  }
+  return R_NONE;
+}
+
+// ---- one window of a Huffman block -------------------------------------------------------------------------
+struct WarpScratch {
+  uint32_t* spec;   // [32][kSpecCap]
+  uint32_t* fix;    // [32][kFixCap]
+  uint16_t* cps;    // [32][kCpPerLane]
+};
+
+DEFL_DEV WarpScratch scratch_of(void* base) {
+  WarpScratch s;
+  s.spec = static_cast<uint32_t*>(base);
+  s.fix  = s.spec + 32u * kSpecCap;
+  s.cps  = reinterpret_cast<uint16_t*>(s.fix + 32u * kFixCap);
+  return s;
+}
+
+// Decode from absolute bit `cur` (a token boundary inside a Huffman block whose tables are in sm) as far
+// as one window reaches.  On return `cur` is where the stream goes on; the result is LS_OK (window done,
+// block goes on), LS_EOB (block ended at cur), or LS_FAIL | reason << 8.
+DEFL_DEV uint32_t decode_window(WarpSmem& sm, const WarpScratch& sc, int lane, const uint32_t* words,
+                                uint32_t wend, uint64_t end_bit, uint64_t& cur, uint8_t* dst, uint32_t cap,
+                                uint32_t& pos) {
+  const uint32_t bw   = (uint32_t)(cur >> 5);
+  const uint32_t rel0 = (uint32_t)(cur & 31u);
+  const uint64_t left64 = end_bit - ((uint64_t)bw << 5);
+  const uint32_t endr = left64 > 0x40000000ull ? 0x40000000u : (uint32_t)left64;   // window-relative end of input
+  const uint32_t remaining = endr - rel0;
+  uint32_t S = (remaining + 31u) / 32u;
+  S = (S + kCpBits - 1u) / kCpBits * kCpBits;
+  S = S < kSubMin ? kSubMin : (S > kSubMax ? kSubMax : S);
+
+  const uint32_t start = rel0 + (uint32_t)lane * S;
+  const uint32_t limit = start + S;
+  const bool     active = start < endr || lane == 0;
+  uint32_t* seg = sc.spec + (uint32_t)lane * kSpecCap;
+  uint32_t* fix = sc.fix + (uint32_t)lane * kFixCap;
+  uint16_t* cps = sc.cps + (uint32_t)lane * kCpPerLane;
+
+  LaneTraj tj;
+  tj.land = start; tj.stat = LS_NONE; tj.n = 0; tj.m = 0; tj.nf = 0; tj.T = start; tj.ncp = 0;
+  tj.s_land = start; tj.s_stat = LS_NONE; tj.s_n = 0;
+  if (active) lane_spec(sm.lit, sm.dist, words, wend, bw, start, limit, endr, seg, cps, tj);
+  simt::syncwarp(kFull);
+
+  // fix-up rounds until every lane starts where its predecessor ended
+#pragma unroll 1
+  for (int round = 0; round < 32; round++) {
+    const uint32_t pland = simt::shfl_up(kFull, tj.land, 1);
+    const uint32_t pstat = simt::shfl_up(kFull, tj.stat, 1);
+    const bool need = lane >= 1 && active && pstat == LS_OK && pland != tj.T;
+    if (!simt::any(kFull, need)) break;
+    if (need) lane_redo(sm.lit, sm.dist, words, wend, bw, start, limit, endr, fix, cps, pland, tj);
+    simt::syncwarp(kFull);
+  }
+
+  // the first lane whose true trajectory stopped ends the window; without one, the last active lane does
+  const unsigned act  = simt::ballot(kFull, active);
+  const unsigned stop = simt::ballot(kFull, active && tj.stat != LS_OK);
+  const int      last = stop ? simt::ffs(stop) - 1 : 31 - simt::clz(act);
+  simt::syncwarp(kFull);
+
+  uint32_t reason = R_NONE;
+#pragma unroll 1
+  for (int L = 0; L <= last && reason == R_NONE; L++) {
+    const uint32_t nf = simt::shfl(kFull, tj.nf, L);
+    const uint32_t m  = simt::shfl(kFull, tj.m, L);
+    const uint32_t n  = simt::shfl(kFull, tj.n, L);
+    if (nf) reason = resolve_tokens(sm.stage, lane, sc.fix + (uint32_t)L * kFixCap, nf, dst, cap, pos);
+    if (reason == R_NONE && n > m)
+      reason = resolve_tokens(sm.stage, lane, sc.spec + (uint32_t)L * kSpecCap + m, n - m, dst, cap, pos);
+  }
+  if (reason) return fail_stat(reason);
+
+  const uint32_t land = simt::shfl(kFull, tj.land, last);
+  const uint32_t stat = simt::shfl(kFull, tj.stat, last);
+  cur = ((uint64_t)bw << 5) + land;
+  if (stat == LS_FULL) return LS_OK;        // a token segment filled up: the next window starts there
+  return stat;
+}
+
+// ---- one stream, start to finish, by one warp ------------------------------------------------------------------
+DEFL_DEV void inflate_stream_warp(WarpSmem& sm, const WarpScratch& sc, int lane, const uint8_t* src,
+                                  uint32_t srclen, uint8_t* dst, uint32_t cap, int flags, StreamOut& out) {
+  Lane<32> L;
+  L.gmask = kFull; L.lane = lane; L.wlane = lane;
+  out.code = -1; out.adler = 1; out.outlen = 0; out.inpos = 0; out.adler_stored = 0; out.info = 0;
+  if (srclen == 0) { out.code = 0; return; }       // all pieces empty => UNZ_OK (infl.c:1547-1550)
+
+  const bool zlib = (flags & 0xFF) == 1;
+  uint32_t   body = 0;
+  if (zlib) {
+    const uint32_t hr = zlib_header(src, srclen, body);
+    if (hr) { out.info = hr << 8; return; }
+  }
+  const uint32_t mis      = (uint32_t)((uintptr_t)src & 3u);
+  const uint64_t base_bit = (uint64_t)mis * 8u;
+  const uint64_t end_bit  = base_bit + (uint64_t)srclen * 8u;
+  BitReader br;
+  br.w    = reinterpret_cast<const uint32_t*>((uintptr_t)src - mis);
+  br.wend = (uint32_t)(((uint64_t)mis + srclen + 3u) >> 2);
+  br.seek(base_bit + body * 8u);
+
+  uint32_t pos = 0, reason = R_NONE;
+  bool     fixed_ready = false;
+#pragma unroll 1
+  for (;;) {
+    if ((int64_t)(end_bit - br.bitpos()) < 3) { reason = R_TRUNCATED; break; }
+    const uint32_t hdr    = br.peek();
+    const uint32_t bfinal = hdr & 1u, btype = (hdr >> 1) & 3u;
+    br.skip(3); br.norm();
+    if (btype == 0) {
+      reason = stored_block<32>(L, br, src, srclen, base_bit, dst, pos, cap);
+      if (reason) break;
+    } else if (btype == 3) {
+      reason = R_BLOCK_TYPE;
+      break;
+    } else {
+      simt::syncwarp(kFull);
+      reason = huffman_block_setup<32>(L, sm.lit, sm.dist, sm.s, br, end_bit, btype, fixed_ready);
+      if (reason) break;
+      simt::syncwarp(kFull);
+      uint64_t cur = br.bitpos();
+      uint32_t st;
+#pragma unroll 1
+      do {
+        st = decode_window(sm, sc, lane, br.w, br.wend, end_bit, cur, dst, cap, pos);
+      } while (st == LS_OK);
+      if (st != LS_EOB) { reason = st >> 8; break; }
+      br.seek(cur);
+    }
+    if (bfinal) break;
+  }
+  if (reason) { out.info = reason << 8; out.outlen = pos; return; }
+
+  uint32_t A = 0, W = 0;
+  simt::syncwarp(kFull);
+  adler_range<32>(L, dst, 0, pos, A, W);
+  finish_stream<32>(L, src, srclen, pos, br.bitpos() - base_bit, A, W, zlib, flags, out);
+}
+
+}  // namespace defl

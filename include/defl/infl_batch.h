@@ -107,6 +107,9 @@ UNZ_EXPORT uint64_t    infl_kernel_launch_count(void);
    pipeline shape: 0..3 = compiled (decoder warps, slots, worker warps) variants */
 UNZ_EXPORT int         infl_set_lanes_per_stream(int lanes);
 UNZ_EXPORT int         infl_set_pipeline_shape(int shape);
+/* decode engine for batches: 3 = one warp per stream, lanes decode sub-sequences speculatively (default);
+   2 = lane-decoder pipeline; 1 = group per stream (uses infl_set_lanes_per_stream) */
+UNZ_EXPORT int         infl_set_engine(int engine);
 
 #ifdef __cplusplus
 }

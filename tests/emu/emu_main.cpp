@@ -3,6 +3,7 @@
 #include "simt_emu.h"
 #include "../../defl_b200/csrc/inflate_core.cuh"
 #include "../../defl_b200/csrc/pipeline.cuh"
+#include "../../defl_b200/csrc/warp_decode.cuh"
 
 #include <stdlib.h>
 #include <vector>
@@ -134,4 +135,53 @@ extern "C" int emu_pipeline(int D, int SL, int K, const infl_batch_item_t* items
   for (int w = 0; w < nw; w++) pthread_barrier_destroy(&c.warps[w].bar);
   free(c.slots); free(c.wsm);
   return 0;
+}
+
+// ---- one emulated warp of the warp-per-stream decoder (warp_decode.cuh) --------------------------------
+namespace {
+
+struct WarpJob {
+  simt::Group*     grp;
+  int              lane;
+  defl::WarpSmem*  sm;
+  void*            scratch;
+  const uint8_t*   src;
+  uint32_t         srclen;
+  uint8_t*         dst;
+  uint32_t         cap;
+  int              flags;
+  defl::StreamOut* out;
+};
+
+void* warp_main(void* arg) {
+  WarpJob* j = static_cast<WarpJob*>(arg);
+  simt::t_group = j->grp;
+  simt::t_lane  = j->lane;
+  defl::StreamOut o;
+  defl::inflate_stream_warp(*j->sm, defl::scratch_of(j->scratch), j->lane, j->src, j->srclen, j->dst, j->cap,
+                            j->flags, o);
+  if (j->lane == 0) *j->out = o;
+  return nullptr;
+}
+
+}  // namespace
+
+extern "C" int emu_warp_inflate(const uint8_t* src, uint32_t srclen, uint8_t* dst, uint32_t cap, int flags,
+                                defl::StreamOut* out) {
+  simt::Group grp;
+  grp.G = 32;
+  pthread_barrier_init(&grp.bar, nullptr, 32);
+  defl::WarpSmem* sm = static_cast<defl::WarpSmem*>(aligned_alloc(64, (sizeof(defl::WarpSmem) + 63) & ~63ul));
+  memset(sm, 0xA5, sizeof(*sm));
+  void* scratch = aligned_alloc(64, defl::kWarpScratchBytes);
+  memset(scratch, 0x5A, defl::kWarpScratchBytes);
+  std::vector<WarpJob>   jobs(32);
+  std::vector<pthread_t> th(32);
+  for (int i = 0; i < 32; i++) jobs[i] = WarpJob{&grp, i, sm, scratch, src, srclen, dst, cap, flags, out};
+  for (int i = 1; i < 32; i++) pthread_create(&th[i], nullptr, warp_main, &jobs[i]);
+  warp_main(&jobs[0]);
+  for (int i = 1; i < 32; i++) pthread_join(th[i], nullptr);
+  pthread_barrier_destroy(&grp.bar);
+  free(sm); free(scratch);
+  return out->code;
 }

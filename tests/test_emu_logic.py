@@ -15,7 +15,8 @@ import oracle_lib as ol
 HERE = os.path.dirname(os.path.abspath(__file__))
 EMU_DIR = os.path.join(HERE, "emu")
 EMU_SO = os.path.join(EMU_DIR, "libemu.so")
-CORE = os.path.join(os.path.dirname(HERE), "defl_b200", "csrc", "inflate_core.cuh")
+CSRC = os.path.join(os.path.dirname(HERE), "defl_b200", "csrc")
+CORE = os.path.join(CSRC, "inflate_core.cuh")
 
 
 class StreamOut(ctypes.Structure):
@@ -25,7 +26,8 @@ class StreamOut(ctypes.Structure):
 
 @pytest.fixture(scope="module")
 def emu():
-    srcs = [os.path.join(EMU_DIR, "emu_main.cpp"), os.path.join(EMU_DIR, "simt_emu.h"), CORE]
+    srcs = [os.path.join(EMU_DIR, "emu_main.cpp"), os.path.join(EMU_DIR, "simt_emu.h"), CORE,
+            os.path.join(CSRC, "pipeline.cuh"), os.path.join(CSRC, "warp_decode.cuh")]
     if not os.path.exists(EMU_SO) or any(os.path.getmtime(s) > os.path.getmtime(EMU_SO) for s in srcs):
         subprocess.check_call(["g++", "-std=c++17", "-O1", "-fPIC", "-shared", "-pthread", "-w",
                                "-o", EMU_SO, srcs[0]])
@@ -114,3 +116,49 @@ def test_pipeline_mutants_logic(emu):
         by[flags][1].append(cap)
     check_pipeline(emu, (2, 5, 3), by[0][0], by[0][1], 0, "mut0")
     check_pipeline(emu, (1, 32, 2), by[1][0], by[1][1], 1, "mut1")
+
+
+# ---- the warp-per-stream decoder (defl_b200/csrc/warp_decode.cuh): one emulated warp ------------------
+def run_warp(emu, data, cap, flags, mis=0):
+    buf = ctypes.create_string_buffer(len(data) + 16)
+    base = ctypes.addressof(buf)
+    off = (-base) % 4 + mis
+    ctypes.memmove(base + off, data, len(data))
+    dst = ctypes.create_string_buffer(cap + 16)
+    o = StreamOut()
+    rc = emu.emu_warp_inflate(ctypes.c_void_p(base + off), len(data), dst, cap, flags, ctypes.byref(o))
+    return rc, dst.raw[: o.outlen], o
+
+
+def test_warp_corpus_logic(emu, corpus):
+    for i, e in enumerate(corpus):
+        rc0, out0, r0 = ol.port_inflate(e["data"], e["cap"], 0)
+        rc, out, o = run_warp(emu, e["data"], e["cap"], 0, mis=i % 4)
+        assert same(rc, out, o, rc0, out0, r0), (e["name"], o.info >> 8)
+
+
+def test_warp_mutants_logic(emu):
+    from test_oracle import _mutants
+    for it, (d, cap, flags, raw, m) in enumerate(_mutants(9001, 500)):
+        rc0, out0, r0 = ol.port_inflate(d, cap, flags)
+        rc, out, o = run_warp(emu, d, cap, flags, mis=it % 4)
+        assert same(rc, out, o, rc0, out0, r0), (it, m, o.info >> 8)
+
+
+def test_warp_large_streams_logic(emu):
+    """Streams long enough for full 32-lane windows, several blocks, every payload class."""
+    from defl_b200 import synth
+    specs = [("text", 300000, 1, 6, zlib.Z_DEFAULT_STRATEGY), ("log", 200000, 2, 9, zlib.Z_DEFAULT_STRATEGY),
+             ("png", 150000, 3, 1, zlib.Z_DEFAULT_STRATEGY), ("rand", 70000, 4, 6, zlib.Z_DEFAULT_STRATEGY),
+             ("zero", 600000, 5, 6, zlib.Z_DEFAULT_STRATEGY), ("text", 120000, 6, 6, zlib.Z_FIXED),
+             ("text", 65536, 7, 6, zlib.Z_DEFAULT_STRATEGY), ("png", 65536, 8, 6, zlib.Z_HUFFMAN_ONLY)]
+    for k, (raw, z) in enumerate(synth.make_streams(specs, threads=1)):
+        rc0, out0, r0 = ol.port_inflate(z, len(raw), 1)
+        assert rc0 == 0 and out0 == raw
+        rc, out, o = run_warp(emu, z, len(raw), 1, mis=k % 4)
+        assert same(rc, out, o, rc0, out0, r0), (k, o.info >> 8)
+        # one byte short of output space, and a truncated input: same verdict as the oracle
+        for d, cap in ((z, len(raw) - 1), (z[: len(z) * 2 // 3], len(raw))):
+            rc0, out0, r0 = ol.port_inflate(d, cap, 1)
+            rc, out, o = run_warp(emu, d, cap, 1)
+            assert rc == rc0 == -1, (k, cap)

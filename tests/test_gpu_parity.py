@@ -13,7 +13,7 @@ import oracle_lib as ol
 
 pytestmark = pytest.mark.gpu
 
-LANES = (0, 1, 2, 4, 8, 16, 32)   # 0 = the default engine (lane-decoder pipeline)
+LANES = (0, 1, 2, 4, 8, 16, 32)   # 0 = the default engine (warp per stream); 1..32 = group per stream
 
 
 def _check_against_port(d, res, outs, datas, caps, flags, what):
@@ -301,6 +301,7 @@ def test_pipeline_shapes(gpu_lib):
     zs = [z for _, z in streams]
     caps = [len(r) for r, _ in streams]
     try:
+        d.set_engine(2)
         for shape in range(8):
             d.set_pipeline_shape(shape)
             res, outs = d.infl_buf_batch(zs, caps, d.INFL_ZLIB | d.INFL_BATCH_VERIFY_ADLER)
@@ -310,3 +311,4 @@ def test_pipeline_shapes(gpu_lib):
                 assert int(res[i]["adler"]) == (zlib.adler32(raw) & 0xFFFFFFFF)
     finally:
         d.set_pipeline_shape(0)
+        d.set_engine(3)
