@@ -63,6 +63,15 @@ struct DevBuf {
     cap = want;
     return UNZ_OK;
   }
+  int reserve_exact(size_t n) {      // no slack: the token scratch is large and never grows
+    if (n <= cap) return UNZ_OK;
+    if (p) cudaFree(p);
+    p = nullptr; cap = 0;
+    cudaError_t e = cudaMalloc(&p, n);
+    if (e != cudaSuccess) return fail("cudaMalloc (workspace)", e);
+    cap = n;
+    return UNZ_OK;
+  }
 };
 
 struct PinBuf {
@@ -259,97 +268,163 @@ constexpr size_t kAlign = 16;
 inline size_t align_up(size_t v) { return (v + kAlign - 1) & ~(kAlign - 1); }
 
 // ---- host-pointer batch on ONE device: stage in, decode, stage out ----------------------------------------
-// Inputs that are adjacent in host memory travel as one copy; so do outputs.
-int run_host_batch_on_device(const infl_batch_item_t* items, size_t n, int flags,
-                             infl_batch_result_t* results) {
-  Engine* E = nullptr;
-  if (engine_for_current_device(&E) != UNZ_OK) return UNZ_ERR;
-  std::lock_guard<std::mutex> guard(E->mu);
-  cudaStream_t st = E->stream;
+// The batch is cut into chunks that run through a two-slot pipeline: while chunk c decodes, chunk c+1's
+// input is on its way to the device and chunk c-1's output on its way back (separate copy engines).
+// Inputs that are (nearly) adjacent in host memory travel as one copy; adjacent outputs do too.
+struct HostRun { const uint8_t* h; size_t len; size_t dev_off; size_t first; size_t count; };
 
-  struct Run { const uint8_t* h; size_t len; size_t dev_off; size_t first; size_t count; };
-  std::vector<Run>    in_runs, out_runs;
-  std::vector<size_t> in_off(n), out_off(n);
+struct PipeSlot {
+  cudaStream_t st = nullptr;
+  DevBuf       d_in, d_out, d_items, d_results, d_order, d_ws;
+  PinBuf       h_items, h_results, h_order;
+  std::vector<HostRun> out_runs;
+  std::vector<size_t>  out_off;
+  size_t first = 0, count = 0;
+};
+
+struct HostPipe {
+  PipeSlot slot[2];
+  bool     ready = false;
+};
+HostPipe g_pipes[kMaxDevices];
+
+constexpr size_t kGapMerge   = 512;          // input runs this close in host memory are copied as one
+constexpr size_t kChunkMin   = 96u << 20;    // bytes (in + out) per chunk, at least
+constexpr size_t kChunkCount = 8;            // aim for this many chunks in a large batch
+
+int chunk_submit(Engine* E, PipeSlot& S, const infl_batch_item_t* items, size_t first, size_t count, int flags) {
+  cudaStream_t st = S.st;
+  std::vector<HostRun> in_runs;
+  std::vector<size_t>  in_off(count);
+  S.out_runs.clear();
+  S.out_off.assign(count, 0);
+  S.first = first; S.count = count;
   size_t in_total = 0, out_total = 0;
-
-  for (size_t i = 0; i < n; i++) {
-    const uint8_t* s = static_cast<const uint8_t*>(items[i].src);
-    if (items[i].srclen > 0xFFFFFFFFull || items[i].dstlen > 0xFFFFFFFFull)
-      return fail("stream larger than 4 GiB - 1 (the reference API limit)");
-    if (!in_runs.empty() && s == in_runs.back().h + in_runs.back().len) {
-      in_off[i] = in_runs.back().dev_off + in_runs.back().len;
-      in_runs.back().len += items[i].srclen;
-      in_runs.back().count++;
+  for (size_t k = 0; k < count; k++) {
+    const infl_batch_item_t& it = items[first + k];
+    const uint8_t* s = static_cast<const uint8_t*>(it.src);
+    if (!in_runs.empty() && s >= in_runs.back().h + in_runs.back().len &&
+        (size_t)(s - (in_runs.back().h + in_runs.back().len)) <= kGapMerge) {
+      // the gap lies between two buffers the caller owns, inside pages they touch: copy it along
+      HostRun& r = in_runs.back();
+      in_off[k] = r.dev_off + (size_t)(s - r.h);
+      r.len = (size_t)(s - r.h) + it.srclen;
+      r.count++;
     } else {
       // keep the device copy congruent to the host pointer mod 16 (same alignment behaviour)
       in_total = align_up(in_total) + ((uintptr_t)s & (kAlign - 1));
-      in_runs.push_back({s, (size_t)items[i].srclen, in_total, i, 1});
-      in_off[i] = in_total;
+      in_runs.push_back({s, (size_t)it.srclen, in_total, k, 1});
+      in_off[k] = in_total;
     }
     in_total = in_runs.back().dev_off + in_runs.back().len;
 
-    const uint8_t* d = static_cast<const uint8_t*>(items[i].dst);
-    if (!out_runs.empty() && d == out_runs.back().h + out_runs.back().len) {
-      out_off[i] = out_runs.back().dev_off + out_runs.back().len;
-      out_runs.back().len += items[i].dstlen;
-      out_runs.back().count++;
+    const uint8_t* d = static_cast<const uint8_t*>(it.dst);
+    if (!S.out_runs.empty() && d == S.out_runs.back().h + S.out_runs.back().len) {
+      S.out_off[k] = S.out_runs.back().dev_off + S.out_runs.back().len;
+      S.out_runs.back().len += it.dstlen;
+      S.out_runs.back().count++;
     } else {
       out_total = align_up(out_total) + ((uintptr_t)d & (kAlign - 1));
-      out_runs.push_back({d, (size_t)items[i].dstlen, out_total, i, 1});
-      out_off[i] = out_total;
+      S.out_runs.push_back({d, (size_t)it.dstlen, out_total, k, 1});
+      S.out_off[k] = out_total;
     }
-    out_total = out_runs.back().dev_off + out_runs.back().len;
+    out_total = S.out_runs.back().dev_off + S.out_runs.back().len;
   }
 
-  if (E->d_in.reserve(in_total + 64) || E->d_out.reserve(out_total + 64) ||
-      E->d_items.reserve(n * sizeof(infl_batch_item_t)) || E->d_results.reserve(n * sizeof(infl_batch_result_t)) ||
-      E->d_order.reserve(n * sizeof(uint32_t)) || E->d_ws.reserve(warp_kernel_workspace(E->sms)) ||
-      E->h_items.reserve(n * sizeof(infl_batch_item_t)) || E->h_results.reserve(n * sizeof(infl_batch_result_t)) ||
-      E->h_order.reserve(n * sizeof(uint32_t)))
+  if (S.d_in.reserve(in_total + 64) || S.d_out.reserve(out_total + 64) ||
+      S.d_items.reserve(count * sizeof(infl_batch_item_t)) || S.d_results.reserve(count * sizeof(infl_batch_result_t)) ||
+      S.d_order.reserve(count * sizeof(uint32_t)) || S.d_ws.reserve_exact(warp_kernel_workspace(E->sms)) ||
+      S.h_items.reserve(count * sizeof(infl_batch_item_t)) || S.h_results.reserve(count * sizeof(infl_batch_result_t)) ||
+      S.h_order.reserve(count * sizeof(uint32_t)))
     return UNZ_ERR;
 
-  auto* hi = static_cast<infl_batch_item_t*>(E->h_items.p);
-  auto* ho = static_cast<uint32_t*>(E->h_order.p);
-  auto* hr = static_cast<infl_batch_result_t*>(E->h_results.p);
-  uint8_t* din  = static_cast<uint8_t*>(E->d_in.p);
-  uint8_t* dout = static_cast<uint8_t*>(E->d_out.p);
-  for (size_t i = 0; i < n; i++) {
-    hi[i].src = din + in_off[i];   hi[i].srclen = items[i].srclen;
-    hi[i].dst = dout + out_off[i]; hi[i].dstlen = items[i].dstlen;
+  auto* hi = static_cast<infl_batch_item_t*>(S.h_items.p);
+  auto* ho = static_cast<uint32_t*>(S.h_order.p);
+  uint8_t* din  = static_cast<uint8_t*>(S.d_in.p);
+  uint8_t* dout = static_cast<uint8_t*>(S.d_out.p);
+  for (size_t k = 0; k < count; k++) {
+    hi[k].src = din + in_off[k];     hi[k].srclen = items[first + k].srclen;
+    hi[k].dst = dout + S.out_off[k]; hi[k].dstlen = items[first + k].dstlen;
   }
-  size_order(items, n, ho);
+  size_order(items + first, count, ho);
 
-  for (const Run& r : in_runs)
+  for (const HostRun& r : in_runs)
     if (r.len) CU_TRY(cudaMemcpyAsync(din + r.dev_off, r.h, r.len, cudaMemcpyHostToDevice, st), "H2D input");
-  CU_TRY(cudaMemcpyAsync(E->d_items.p, hi, n * sizeof(*hi), cudaMemcpyHostToDevice, st), "H2D descriptors");
-  CU_TRY(cudaMemcpyAsync(E->d_order.p, ho, n * sizeof(*ho), cudaMemcpyHostToDevice, st), "H2D order");
-
-  if (launch_batch_any(E->sms, static_cast<infl_batch_item_t*>(E->d_items.p), static_cast<uint32_t*>(E->d_order.p),
-                       n, flags, static_cast<infl_batch_result_t*>(E->d_results.p), E->d_ws.p, st) != UNZ_OK)
+  CU_TRY(cudaMemcpyAsync(S.d_items.p, hi, count * sizeof(*hi), cudaMemcpyHostToDevice, st), "H2D descriptors");
+  CU_TRY(cudaMemcpyAsync(S.d_order.p, ho, count * sizeof(*ho), cudaMemcpyHostToDevice, st), "H2D order");
+  if (launch_batch_any(E->sms, static_cast<infl_batch_item_t*>(S.d_items.p), static_cast<uint32_t*>(S.d_order.p),
+                       count, flags, static_cast<infl_batch_result_t*>(S.d_results.p), S.d_ws.p, st) != UNZ_OK)
     return UNZ_ERR;
+  CU_TRY(cudaMemcpyAsync(S.h_results.p, S.d_results.p, count * sizeof(infl_batch_result_t), cudaMemcpyDeviceToHost, st),
+         "D2H results");
+  return UNZ_OK;
+}
 
-  CU_TRY(cudaMemcpyAsync(hr, E->d_results.p, n * sizeof(*hr), cudaMemcpyDeviceToHost, st), "D2H results");
+// wait for the chunk's results, then send its outputs home (asynchronously on the slot's stream)
+int chunk_finish(PipeSlot& S, const infl_batch_item_t* items, infl_batch_result_t* results) {
+  cudaStream_t st = S.st;
   CU_TRY(cudaStreamSynchronize(st), "inflate kernel");
-
-  // outputs: a whole run in one copy when every stream filled its buffer exactly,
-  // otherwise only the bytes each stream produced
-  for (const Run& r : out_runs) {
+  auto* hr = static_cast<infl_batch_result_t*>(S.h_results.p);
+  uint8_t* dout = static_cast<uint8_t*>(S.d_out.p);
+  // a whole run in one copy when every stream filled its buffer exactly, otherwise only the bytes each produced
+  for (const HostRun& r : S.out_runs) {
     bool exact = r.len != 0;
     for (size_t k = r.first; exact && k < r.first + r.count; k++)
-      exact = hr[k].code == UNZ_OK && hr[k].outlen == items[k].dstlen;
+      exact = hr[k].code == UNZ_OK && hr[k].outlen == items[S.first + k].dstlen;
     if (exact) {
       CU_TRY(cudaMemcpyAsync(const_cast<uint8_t*>(r.h), dout + r.dev_off, r.len, cudaMemcpyDeviceToHost, st),
              "D2H output");
     } else {
       for (size_t k = r.first; k < r.first + r.count; k++)
         if (hr[k].outlen)
-          CU_TRY(cudaMemcpyAsync(items[k].dst, dout + out_off[k], hr[k].outlen, cudaMemcpyDeviceToHost, st),
+          CU_TRY(cudaMemcpyAsync(items[S.first + k].dst, dout + S.out_off[k], hr[k].outlen, cudaMemcpyDeviceToHost, st),
                  "D2H output");
     }
   }
-  CU_TRY(cudaStreamSynchronize(st), "D2H output");
-  std::memcpy(results, hr, n * sizeof(*hr));
+  std::memcpy(results + S.first, hr, S.count * sizeof(*hr));
   return UNZ_OK;
+}
+
+int run_host_batch_on_device(const infl_batch_item_t* items, size_t n, int flags,
+                             infl_batch_result_t* results) {
+  Engine* E = nullptr;
+  if (engine_for_current_device(&E) != UNZ_OK) return UNZ_ERR;
+  std::lock_guard<std::mutex> guard(E->mu);
+  HostPipe& HP = g_pipes[E->dev];
+  if (!HP.ready) {
+    for (PipeSlot& S : HP.slot) CU_TRY(cudaStreamCreateWithFlags(&S.st, cudaStreamNonBlocking), "cudaStreamCreate");
+    HP.ready = true;
+  }
+
+  size_t total = 0;
+  for (size_t i = 0; i < n; i++) {
+    if (items[i].srclen > 0xFFFFFFFFull || items[i].dstlen > 0xFFFFFFFFull)
+      return fail("stream larger than 4 GiB - 1 (the reference API limit)");
+    total += items[i].srclen + items[i].dstlen;
+  }
+  const size_t chunk_bytes = std::max(kChunkMin, total / kChunkCount + 1);
+
+  size_t first = 0;
+  int    c = 0, rc = UNZ_OK;
+  while (first < n && rc == UNZ_OK) {
+    size_t count = 0, bytes = 0;
+    while (first + count < n && (count == 0 || bytes < chunk_bytes)) {
+      bytes += items[first + count].srclen + items[first + count].dstlen;
+      count++;
+    }
+    PipeSlot& S = HP.slot[c & 1];
+    if (c >= 2) rc = (cudaStreamSynchronize(S.st) == cudaSuccess) ? UNZ_OK : fail("D2H output");   // chunk c-2 is home
+    if (rc == UNZ_OK) rc = chunk_submit(E, S, items, first, count, flags);
+    if (rc == UNZ_OK && c >= 1) rc = chunk_finish(HP.slot[(c - 1) & 1], items, results);
+    first += count;
+    c++;
+  }
+  if (rc == UNZ_OK && c >= 1) rc = chunk_finish(HP.slot[(c - 1) & 1], items, results);
+  for (PipeSlot& S : HP.slot) {
+    const cudaError_t e = cudaStreamSynchronize(S.st);
+    if (e != cudaSuccess && rc == UNZ_OK) rc = fail("D2H output", e);
+  }
+  return rc;
 }
 
 // ---- device-pointer batch: only descriptors and results cross the bus ---------------------------------------
@@ -359,7 +434,7 @@ int run_device_batch(const infl_batch_item_t* items, size_t n, int flags, infl_b
   std::lock_guard<std::mutex> guard(E->mu);
   cudaStream_t st = E->stream;
   if (E->d_items.reserve(n * sizeof(infl_batch_item_t)) || E->d_results.reserve(n * sizeof(infl_batch_result_t)) ||
-      E->d_order.reserve(n * sizeof(uint32_t)) || E->d_ws.reserve(warp_kernel_workspace(E->sms)) ||
+      E->d_order.reserve(n * sizeof(uint32_t)) || E->d_ws.reserve_exact(warp_kernel_workspace(E->sms)) ||
       E->h_order.reserve(n * sizeof(uint32_t)))
     return UNZ_ERR;
   auto* ho = static_cast<uint32_t*>(E->h_order.p);
@@ -608,7 +683,7 @@ UNZ_EXPORT int infl_buf_batch_iov(const infl_batch_iov_item_t* items, size_t n, 
       flat[i].dstlen = items[i].dstlen;
     }
     if (E->d_items.reserve(n * sizeof(infl_batch_item_t)) || E->d_results.reserve(n * sizeof(infl_batch_result_t)) ||
-        E->d_order.reserve(n * sizeof(uint32_t)) || E->d_ws.reserve(warp_kernel_workspace(E->sms)) || E->h_order.reserve(n * sizeof(uint32_t)))
+        E->d_order.reserve(n * sizeof(uint32_t)) || E->d_ws.reserve_exact(warp_kernel_workspace(E->sms)) || E->h_order.reserve(n * sizeof(uint32_t)))
       return UNZ_ERR;
     auto* ho = static_cast<uint32_t*>(E->h_order.p);
     size_order(flat.data(), n, ho);

@@ -62,6 +62,7 @@ DEFL_DEV uint32_t ld_out8(const uint8_t* p) { return __ldcg(p); }
 // ---- used by the warp-per-stream decoder (warp_decode.cuh) ------------------------------------------
 DEFL_DEV bool     any(unsigned mask, bool p) { return __any_sync(mask, p); }
 DEFL_DEV int      clz(uint32_t v) { return __clz((int)v); }
+DEFL_DEV uint32_t reduce_add(unsigned mask, uint32_t v) { return __reduce_add_sync(mask, v); }
 // tokens written to the global scratch by one lane and read back by the whole warp: L2 only
 DEFL_DEV uint32_t ld_tok(const uint32_t* p) { return __ldcg(p); }
 

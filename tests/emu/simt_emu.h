@@ -10,6 +10,8 @@
 #include <sched.h>
 #include <stdint.h>
 #include <string.h>
+#include <algorithm>
+using std::max;
 
 #define DEFL_DEV inline
 #define DEFL_DEV_NOINLINE inline
@@ -108,6 +110,14 @@ inline long long ticks() { return 0; }
 inline uint32_t ld_out8(const uint8_t* p) { return *(const volatile uint8_t*)p; }
 inline bool any(unsigned mk, bool p) { return ballot(mk, p) != 0u; }
 inline int clz(uint32_t v) { return v ? __builtin_clz(v) : 32; }
+inline uint32_t reduce_add(unsigned, uint32_t v) {
+  t_group->xchg[t_lane] = v;
+  barrier();
+  uint32_t r = 0;
+  for (int i = 0; i < t_group->G; i++) r += t_group->xchg[i];
+  barrier();
+  return r;
+}
 inline uint32_t ld_tok(const uint32_t* p) { return *(const volatile uint32_t*)p; }
 
 }  // namespace simt
