@@ -129,20 +129,63 @@ struct LaneTraj {
   uint32_t s_land, s_stat, s_n;   // how the speculative trajectory ended (valid again after any later merge)
 };
 
-// speculative pass: decode from `start` (window-relative bits) to `limit`
+// speculative pass: decode from `start` (window-relative bits) to `limit`.
+// The inner loop is the hot loop of the whole engine, so it is written for the instruction count: no
+// end-of-input arithmetic (it stops 64 bits short of the end; decode_token() takes over there, and for
+// anything unusual -- end of block, a pattern no code maps to), one code path for "length + distance" and
+// "literal + maybe a second literal" (the second lookup goes to lit[] or dist[] by index, not by branch),
+// running pointers for the token and checkpoint stores.
 DEFL_DEV void lane_spec(const uint16_t* lit, const uint16_t* dist, const uint32_t* words, uint32_t wend,
                         uint32_t bw, uint32_t start, uint32_t limit, uint32_t endr, uint32_t* seg,
                         uint16_t* cps, LaneTraj& tj) {
   SubReader br;
   br.w = words; br.wend = wend;
   br.seek(bw, start);
-  uint32_t r = start, t = 0, k = 0, next_cp = start, stat = LS_OK;
+  uint32_t        r = start, next_cp = start, stat = LS_OK;
+  uint32_t*       tp = seg;
+  uint32_t* const tend = seg + kSpecCap;
+  uint16_t*       cpp = cps;
+  const uint32_t  fast_limit = endr >= 64u ? (limit < endr - 64u ? limit : endr - 64u) : 0u;
+  const uint32_t  dist_at = (uint32_t)(dist - lit);          // dist[] follows lit[] in shared memory
   for (;;) {
+    // ---- fast loop
+    while (r < fast_limit && tp != tend) {
+      const uint32_t v0 = simt::funnel_r(br.w0, br.w1, br.bo);
+      const uint32_t v1 = simt::funnel_r(br.w1, br.w2, br.bo);
+      uint32_t       e  = lit[v0 & (kLitRoot - 1)];
+      if ((e & (kLitIsLen | kLitKind)) == kLitSub)
+        e = lit[kLitRoot + (e & 0x1FFu) + ((v0 >> kLitRootBits) & ((1u << ((e >> 11) & 15u)) - 1u))];
+      if (e < 0x0800u || (e & (kLitIsLen | kLitKind)) == kLitEob) break;   // no code here / end of block
+      const bool     is_len = (e & kLitIsLen) != 0u;
+      const uint32_t cl   = (e >> 11) & 15u;
+      const uint32_t xb   = (e >> 8) & 7u;                        // 0 for a literal
+      const uint32_t val  = (e & 255u) + simt::bfe(v0, cl, xb);   // byte, or length - 3
+      const uint32_t use1 = cl + xb;
+      const uint32_t v2   = simt::funnel_r(v0, v1, use1);         // the 32 bits after this symbol
+      uint32_t       x    = lit[is_len ? dist_at + (v2 & (kDistRoot - 1)) : (v2 & (kLitRoot - 1))];
+      if (is_len && (x & kDistSub))
+        x = dist[kDistRoot + (x & 0x1FFu) + ((v2 >> kDistRootBits) & ((1u << ((x >> 11) & 15u)) - 1u))];
+      if (is_len && x == 0u) break;                               // no distance code here
+      const uint32_t xcl = (x >> 11) & 15u;
+      const uint32_t dxb = (x >> 7) & 15u;
+      const uint32_t d1  = ((x & 3u) << dxb) + simt::bfe(v2, xcl, dxb);          // distance - 1
+      const bool     two = (x & (kLitIsLen | kLitKind)) == 0u && x >= 0x0800u;   // a second literal follows
+      const uint32_t tok = is_len ? (kTokIsMatch | (d1 << 9) | (val + 3u))
+                                  : (two ? ((2u << 24) | ((x & 255u) << 8) | val) : ((1u << 24) | val));
+      const uint32_t used = use1 + (is_len ? xcl + dxb : (two ? xcl : 0u));
+      if (r >= next_cp) {
+        *cpp++ = (uint16_t)((r - next_cp) | ((uint32_t)(tp - seg) << 6));
+        next_cp += kCpBits;
+      }
+      *tp++ = tok;
+      r += used;
+      br.consume(used);
+    }
+    // ---- one careful step: the ends of the sub-sequence, the input and the block, failures
     if (r >= limit) break;
-    if (t == kSpecCap) { stat = LS_FULL; break; }
+    if (tp == tend) { stat = LS_FULL; break; }
     if (r >= next_cp) {
-      cps[k] = (uint16_t)((r - next_cp) | (t << 6));
-      k++;
+      *cpp++ = (uint16_t)((r - next_cp) | ((uint32_t)(tp - seg) << 6));
       next_cp += kCpBits;
     }
     uint32_t tok, used;
@@ -152,11 +195,12 @@ DEFL_DEV void lane_spec(const uint16_t* lit, const uint16_t* dist, const uint32_
       if (s == LS_EOB) r += used;
       break;
     }
-    seg[t++] = tok;
+    *tp++ = tok;
     r += used;
     br.consume(used);
   }
-  tj.land = r; tj.stat = stat; tj.n = t; tj.m = 0; tj.nf = 0; tj.T = start; tj.ncp = k;
+  const uint32_t t = (uint32_t)(tp - seg);
+  tj.land = r; tj.stat = stat; tj.n = t; tj.m = 0; tj.nf = 0; tj.T = start; tj.ncp = (uint32_t)(cpp - cps);
   tj.s_land = r; tj.s_stat = stat; tj.s_n = t;
 }
 
