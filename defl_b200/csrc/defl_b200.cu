@@ -267,6 +267,172 @@ void size_order(const infl_batch_item_t* items, size_t n, uint32_t* order) {
 constexpr size_t kAlign = 16;
 inline size_t align_up(size_t v) { return (v + kAlign - 1) & ~(kAlign - 1); }
 
+// ---- one large stream, decoded by the whole GPU (split_decode.cuh) ----------------------------------------------
+constexpr uint64_t kSplitMinBytes = 4ull << 20;      // compressed size from which a stream is worth splitting
+constexpr uint64_t kSplitMinGap   = 40960ull * 8;    // bits between chosen block starts: chunks produce >= 32 KiB
+std::atomic<uint64_t> g_split_decodes{0};
+
+struct SplitBufs {
+  DevBuf d_found, d_cand, d_jobs, d_outs, d_sym, d_off, d_partial;
+};
+SplitBufs g_split[kMaxDevices];
+
+// Returns UNZ_OK with *res filled when the split path decoded the stream, UNZ_NOOP when the stream has to go
+// through the one-warp decoder instead (too few block starts, any failure: that path defines error behaviour),
+// UNZ_ERR when the engine itself failed.  d_src / d_dst are device pointers; d_ws is the token scratch.
+int split_decode_device(Engine* E, const uint8_t* d_src, uint64_t srclen, uint8_t* d_dst, uint64_t dstlen, int flags,
+                        void* d_ws, cudaStream_t st, infl_batch_result_t* res) {
+  using namespace defl;
+  SplitBufs& SB = g_split[E->dev];
+  const bool zlib = (flags & 0xFF) == INFL_ZLIB;
+  uint32_t   body = 0;
+  if (zlib) {
+    uint8_t h2[2];
+    CU_TRY(cudaMemcpyAsync(h2, d_src, 2, cudaMemcpyDeviceToHost, st), "D2H zlib header");
+    CU_TRY(cudaStreamSynchronize(st), "D2H zlib header");
+    if ((h2[0] & 15) != 8 || (h2[0] >> 4) > 7 || ((h2[0] << 8) + h2[1]) % 31 != 0 || (h2[1] & 0x20)) return UNZ_NOOP;
+    body = 2;
+  }
+  int grid_warps = 0;
+  if (warp_kernel_grid(E->sms, &grid_warps) != UNZ_OK) return UNZ_ERR;      // CTAs of kWarpsPerCta warps
+  auto* ticket  = static_cast<unsigned int*>(d_ws);
+  auto* scratch = static_cast<unsigned char*>(d_ws) + kWsHeader;
+  const size_t smem = sizeof(WarpSmem) * kWarpsPerCta;
+
+  // ---- F: block starts
+  const uint32_t ngran = (uint32_t)((srclen - body + kGranuleBytes - 1) / kGranuleBytes);
+  if (SB.d_found.reserve((size_t)ngran * 8)) return UNZ_ERR;
+  {
+    auto kern = find_block_starts_kernel<kWarpsPerCta>;
+    static bool attr_done[kMaxDevices] = {false};
+    if (!attr_done[E->dev]) {
+      CU_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem), "cudaFuncSetAttribute");
+      attr_done[E->dev] = true;
+    }
+    kern<<<(ngran + kWarpsPerCta - 1) / kWarpsPerCta, kWarpsPerCta * 32, smem, st>>>(
+        d_src, (uint32_t)srclen, body, ngran, static_cast<uint64_t*>(SB.d_found.p));
+    CU_TRY(cudaGetLastError(), "find_block_starts_kernel launch");
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+  }
+  std::vector<uint64_t> found(ngran);
+  CU_TRY(cudaMemcpyAsync(found.data(), SB.d_found.p, (size_t)ngran * 8, cudaMemcpyDeviceToHost, st), "D2H block starts");
+  CU_TRY(cudaStreamSynchronize(st), "find_block_starts_kernel");
+  std::vector<uint64_t> cand;
+  cand.push_back((uint64_t)body * 8);
+  for (uint64_t f : found)
+    if (f != kNoCandidate && f >= cand.back() + kSplitMinGap) cand.push_back(f);
+  const uint32_t ncand = (uint32_t)cand.size();
+  if (ncand < 8) return UNZ_NOOP;
+
+  // ---- A: every candidate counts its chunk
+  std::vector<SplitJob> jobs(ncand);
+  for (uint32_t i = 0; i < ncand; i++) { jobs[i].cand = i; jobs[i].cap = 0; jobs[i].out_off = 0; }
+  if (SB.d_cand.reserve((size_t)ncand * 8) || SB.d_jobs.reserve((size_t)ncand * sizeof(SplitJob)) ||
+      SB.d_outs.reserve((size_t)ncand * sizeof(SplitChunkOut)))
+    return UNZ_ERR;
+  CU_TRY(cudaMemcpyAsync(SB.d_cand.p, cand.data(), (size_t)ncand * 8, cudaMemcpyHostToDevice, st), "H2D candidates");
+  CU_TRY(cudaMemcpyAsync(SB.d_jobs.p, jobs.data(), (size_t)ncand * sizeof(SplitJob), cudaMemcpyHostToDevice, st), "H2D jobs");
+  auto launch_chunks = [&](bool count, uint32_t njobs, uint16_t* sym) -> int {
+    static bool attr_done[kMaxDevices][2] = {};
+    if (!attr_done[E->dev][count]) {
+      if (count) CU_TRY(cudaFuncSetAttribute(split_chunk_kernel<true, kWarpsPerCta>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem), "cudaFuncSetAttribute");
+      else CU_TRY(cudaFuncSetAttribute(split_chunk_kernel<false, kWarpsPerCta>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem), "cudaFuncSetAttribute");
+      attr_done[E->dev][count] = true;
+    }
+    const unsigned grid = (unsigned)std::max<uint32_t>(1, std::min<uint32_t>((uint32_t)grid_warps, (njobs + kWarpsPerCta - 1) / kWarpsPerCta));
+    CU_TRY(cudaMemsetAsync(ticket, 0, sizeof(unsigned int), st), "cudaMemsetAsync(ticket)");
+    if (count)
+      split_chunk_kernel<true, kWarpsPerCta><<<grid, kWarpsPerCta * 32, smem, st>>>(
+          d_src, (uint32_t)srclen, static_cast<uint64_t*>(SB.d_cand.p), ncand, static_cast<SplitJob*>(SB.d_jobs.p), njobs,
+          sym, static_cast<SplitChunkOut*>(SB.d_outs.p), ticket, scratch);
+    else
+      split_chunk_kernel<false, kWarpsPerCta><<<grid, kWarpsPerCta * 32, smem, st>>>(
+          d_src, (uint32_t)srclen, static_cast<uint64_t*>(SB.d_cand.p), ncand, static_cast<SplitJob*>(SB.d_jobs.p), njobs,
+          sym, static_cast<SplitChunkOut*>(SB.d_outs.p), ticket, scratch);
+    CU_TRY(cudaGetLastError(), "split_chunk_kernel launch");
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+    return UNZ_OK;
+  };
+  if (launch_chunks(true, ncand, nullptr) != UNZ_OK) return UNZ_ERR;
+  std::vector<SplitChunkOut> outs(ncand);
+  CU_TRY(cudaMemcpyAsync(outs.data(), SB.d_outs.p, (size_t)ncand * sizeof(SplitChunkOut), cudaMemcpyDeviceToHost, st), "D2H chunk sizes");
+  CU_TRY(cudaStreamSynchronize(st), "split_chunk_kernel (count)");
+
+  // ---- the chain of true chunks, from the stream's first block to its final block
+  std::vector<uint32_t> chain;
+  std::vector<uint64_t> off;
+  uint64_t total = 0, end_bit = 0;
+  for (uint32_t i = 0;;) {
+    const SplitChunkOut& o = outs[i];
+    if ((o.status & 0xFF) == CH_FAIL) return UNZ_NOOP;
+    chain.push_back(i);
+    off.push_back(total);
+    total += o.out_bytes;
+    if (total > dstlen || total > 0xFFFFFFFFull) return UNZ_NOOP;
+    if (o.status == CH_FINAL) { end_bit = o.end_bit; break; }
+    if (o.link <= i || o.link >= ncand) return UNZ_NOOP;
+    i = o.link;
+  }
+  off.push_back(total);
+  const uint32_t nchunk = (uint32_t)chain.size();
+
+  // ---- C: the chain decodes into 16-bit symbols at final offsets
+  for (uint32_t k = 0; k < nchunk; k++) {
+    jobs[k].cand = chain[k]; jobs[k].cap = outs[chain[k]].out_bytes; jobs[k].out_off = off[k];
+  }
+  if (SB.d_sym.reserve((size_t)total * 2 + 64) || SB.d_off.reserve((size_t)(nchunk + 1) * 8)) return UNZ_ERR;
+  CU_TRY(cudaMemcpyAsync(SB.d_jobs.p, jobs.data(), (size_t)nchunk * sizeof(SplitJob), cudaMemcpyHostToDevice, st), "H2D jobs");
+  CU_TRY(cudaMemcpyAsync(SB.d_off.p, off.data(), (size_t)(nchunk + 1) * 8, cudaMemcpyHostToDevice, st), "H2D offsets");
+  if (launch_chunks(false, nchunk, static_cast<uint16_t*>(SB.d_sym.p)) != UNZ_OK) return UNZ_ERR;
+  std::vector<SplitChunkOut> outs2(nchunk);
+  CU_TRY(cudaMemcpyAsync(outs2.data(), SB.d_outs.p, (size_t)nchunk * sizeof(SplitChunkOut), cudaMemcpyDeviceToHost, st), "D2H chunk results");
+
+  // ---- D: markers -> bytes, Adler-32
+  const uint32_t nblk = (uint32_t)((total + 4095) / 4096);
+  std::vector<uint32_t> partial((size_t)nblk * 2);
+  if (nblk) {
+    if (SB.d_partial.reserve((size_t)nblk * 8)) return UNZ_ERR;
+    marker_resolve_kernel<<<nblk, 256, 0, st>>>(static_cast<uint16_t*>(SB.d_sym.p), static_cast<uint64_t*>(SB.d_off.p), nchunk,
+                                                 d_dst, total, static_cast<uint32_t*>(SB.d_partial.p));
+    CU_TRY(cudaGetLastError(), "marker_resolve_kernel launch");
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+    CU_TRY(cudaMemcpyAsync(partial.data(), SB.d_partial.p, (size_t)nblk * 8, cudaMemcpyDeviceToHost, st), "D2H adler partials");
+  }
+  uint8_t trailer[4] = {0, 0, 0, 0};
+  const uint64_t inpos = (end_bit + 7) >> 3;
+  const bool has_trailer = zlib && srclen - inpos >= 4;
+  if (has_trailer) CU_TRY(cudaMemcpyAsync(trailer, d_src + inpos, 4, cudaMemcpyDeviceToHost, st), "D2H trailer");
+  CU_TRY(cudaStreamSynchronize(st), "split decode");
+  for (uint32_t k = 0; k < nchunk; k++)
+    if (outs2[k].status != outs[chain[k]].status || outs2[k].out_bytes != outs[chain[k]].out_bytes ||
+        outs2[k].end_bit != outs[chain[k]].end_bit)
+      return UNZ_NOOP;            // cannot happen for a deterministic decode; the one-warp decoder has the last word
+
+  uint64_t sa = 0, sw = 0;
+  for (uint32_t b = 0; b < nblk; b++) { sa += partial[2 * b]; sw += partial[2 * b + 1]; }
+  sa %= defl::kAdlerMod; sw %= defl::kAdlerMod;
+  const uint64_t nm = total % defl::kAdlerMod;
+  const uint32_t a = (uint32_t)((1 + sa) % defl::kAdlerMod);
+  const uint32_t b = (uint32_t)((nm + nm * sa + defl::kAdlerMod - sw) % defl::kAdlerMod);
+  std::memset(res, 0, sizeof(*res));
+  res->code = UNZ_OK;
+  res->adler = (b << 16) | a;
+  res->outlen = total;
+  res->inpos = inpos;
+  res->info = INFL_INFO_SPLIT_DECODE;
+  if (has_trailer) {
+    res->adler_stored = ((uint32_t)trailer[0] << 24) | ((uint32_t)trailer[1] << 16) | ((uint32_t)trailer[2] << 8) | trailer[3];
+    res->info |= INFL_INFO_HAS_TRAILER;
+    if (res->adler_stored == res->adler) res->info |= INFL_INFO_ADLER_MATCH;
+  }
+  if (zlib && (flags & INFL_BATCH_VERIFY_ADLER) && (res->info & 3u) != 3u) {
+    res->code = UNZ_ERR;
+    res->info |= defl::R_ADLER << INFL_INFO_REASON_SHIFT;
+  }
+  g_split_decodes.fetch_add(1, std::memory_order_relaxed);
+  return UNZ_OK;
+}
+
 // ---- host-pointer batch on ONE device: stage in, decode, stage out ----------------------------------------
 // The batch is cut into chunks that run through a two-slot pipeline: while chunk c decodes, chunk c+1's
 // input is on its way to the device and chunk c-1's output on its way back (separate copy engines).
@@ -389,7 +555,7 @@ int run_host_batch_on_device(const infl_batch_item_t* items, size_t n, int flags
                              infl_batch_result_t* results) {
   Engine* E = nullptr;
   if (engine_for_current_device(&E) != UNZ_OK) return UNZ_ERR;
-  std::lock_guard<std::mutex> guard(E->mu);
+  std::unique_lock<std::mutex> guard(E->mu);
   HostPipe& HP = g_pipes[E->dev];
   if (!HP.ready) {
     for (PipeSlot& S : HP.slot) CU_TRY(cudaStreamCreateWithFlags(&S.st, cudaStreamNonBlocking), "cudaStreamCreate");
@@ -401,6 +567,41 @@ int run_host_batch_on_device(const infl_batch_item_t* items, size_t n, int flags
     if (items[i].srclen > 0xFFFFFFFFull || items[i].dstlen > 0xFFFFFFFFull)
       return fail("stream larger than 4 GiB - 1 (the reference API limit)");
     total += items[i].srclen + items[i].dstlen;
+  }
+  // large streams first, one at a time, through the split-point decoder (they fill the GPU on their own)
+  if (!(flags & INFL_BATCH_NO_SPLIT)) {
+    bool any = false;
+    for (size_t i = 0; i < n; i++) any = any || items[i].srclen >= kSplitMinBytes;
+    if (any) {
+      std::vector<infl_batch_item_t> rest;
+      std::vector<size_t>            rest_idx;
+      PipeSlot& S = HP.slot[0];
+      for (size_t i = 0; i < n; i++) {
+        int rc = UNZ_NOOP;
+        if (items[i].srclen >= kSplitMinBytes) {
+          if (S.d_in.reserve(items[i].srclen + 64) || S.d_out.reserve(items[i].dstlen + 64) ||
+              S.d_ws.reserve_exact(warp_kernel_workspace(E->sms)))
+            return UNZ_ERR;
+          // same alignment of the device copy as the host pointer's
+          uint8_t* din = static_cast<uint8_t*>(S.d_in.p) + ((uintptr_t)items[i].src & (kAlign - 1));
+          CU_TRY(cudaMemcpyAsync(din, items[i].src, items[i].srclen, cudaMemcpyHostToDevice, S.st), "H2D input");
+          rc = split_decode_device(E, din, items[i].srclen, static_cast<uint8_t*>(S.d_out.p), items[i].dstlen, flags,
+                                   S.d_ws.p, S.st, &results[i]);
+          if (rc == UNZ_ERR) return UNZ_ERR;
+          if (rc == UNZ_OK && results[i].outlen) {
+            CU_TRY(cudaMemcpyAsync(items[i].dst, S.d_out.p, results[i].outlen, cudaMemcpyDeviceToHost, S.st), "D2H output");
+            CU_TRY(cudaStreamSynchronize(S.st), "D2H output");
+          }
+        }
+        if (rc == UNZ_NOOP) { rest.push_back(items[i]); rest_idx.push_back(i); }
+      }
+      if (rest.empty()) return UNZ_OK;
+      std::vector<infl_batch_result_t> rr(rest.size());
+      guard.unlock();
+      const int rc2 = run_host_batch_on_device(rest.data(), rest.size(), flags | INFL_BATCH_NO_SPLIT, rr.data());
+      for (size_t k = 0; k < rr.size(); k++) results[rest_idx[k]] = rr[k];
+      return rc2;
+    }
   }
   const size_t chunk_bytes = std::max(kChunkMin, total / kChunkCount + 1);
 
@@ -437,6 +638,36 @@ int run_device_batch(const infl_batch_item_t* items, size_t n, int flags, infl_b
       E->d_order.reserve(n * sizeof(uint32_t)) || E->d_ws.reserve_exact(warp_kernel_workspace(E->sms)) ||
       E->h_order.reserve(n * sizeof(uint32_t)))
     return UNZ_ERR;
+  // large streams go through the split-point decoder, one after another; the rest is one batch launch
+  std::vector<infl_batch_item_t> rest;
+  std::vector<size_t>            rest_idx;
+  bool any_split = false;
+  if (!(flags & INFL_BATCH_NO_SPLIT))
+    for (size_t i = 0; i < n; i++)
+      if (items[i].srclen >= kSplitMinBytes && items[i].srclen <= 0xFFFFFFFFull && items[i].dstlen <= 0xFFFFFFFFull) any_split = true;
+  if (any_split) {
+    for (size_t i = 0; i < n; i++) {
+      int rc = UNZ_NOOP;
+      if (items[i].srclen >= kSplitMinBytes && items[i].srclen <= 0xFFFFFFFFull && items[i].dstlen <= 0xFFFFFFFFull)
+        rc = split_decode_device(E, static_cast<const uint8_t*>(items[i].src), items[i].srclen,
+                                 static_cast<uint8_t*>(items[i].dst), items[i].dstlen, flags, E->d_ws.p, st, &results[i]);
+      if (rc == UNZ_ERR) return UNZ_ERR;
+      if (rc == UNZ_NOOP) { rest.push_back(items[i]); rest_idx.push_back(i); }
+    }
+    if (rest.empty()) return UNZ_OK;
+    std::vector<infl_batch_result_t> rr(rest.size());
+    auto* ho2 = static_cast<uint32_t*>(E->h_order.p);
+    size_order(rest.data(), rest.size(), ho2);
+    CU_TRY(cudaMemcpyAsync(E->d_items.p, rest.data(), rest.size() * sizeof(rest[0]), cudaMemcpyHostToDevice, st), "H2D descriptors");
+    CU_TRY(cudaMemcpyAsync(E->d_order.p, ho2, rest.size() * sizeof(*ho2), cudaMemcpyHostToDevice, st), "H2D order");
+    if (launch_batch_any(E->sms, static_cast<infl_batch_item_t*>(E->d_items.p), static_cast<uint32_t*>(E->d_order.p),
+                         rest.size(), flags, static_cast<infl_batch_result_t*>(E->d_results.p), E->d_ws.p, st) != UNZ_OK)
+      return UNZ_ERR;
+    CU_TRY(cudaMemcpyAsync(rr.data(), E->d_results.p, rr.size() * sizeof(rr[0]), cudaMemcpyDeviceToHost, st), "D2H results");
+    CU_TRY(cudaStreamSynchronize(st), "inflate kernel");
+    for (size_t k = 0; k < rr.size(); k++) results[rest_idx[k]] = rr[k];
+    return UNZ_OK;
+  }
   auto* ho = static_cast<uint32_t*>(E->h_order.p);
   size_order(items, n, ho);
   CU_TRY(cudaMemcpyAsync(E->d_items.p, items, n * sizeof(*items), cudaMemcpyHostToDevice, st), "H2D descriptors");

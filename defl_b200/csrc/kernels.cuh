@@ -4,6 +4,7 @@
 #include "inflate_core.cuh"
 #include "pipeline.cuh"
 #include "warp_decode.cuh"
+#include "split_decode.cuh"
 #include "../../include/defl/infl_batch.h"
 
 namespace defl {

@@ -58,6 +58,8 @@ DEFL_DEV long long ticks() { return clock64(); }
 // decoded output read back as a match source: written earlier by this SM, cached at L2 only so the
 // L1 stays with the compressed input lines the decoder lanes stream through
 DEFL_DEV uint32_t ld_out8(const uint8_t* p) { return __ldcg(p); }
+DEFL_DEV uint32_t ld_out(const uint8_t* p) { return __ldcg(p); }
+DEFL_DEV uint32_t ld_out(const uint16_t* p) { return __ldcg(p); }
 
 // ---- used by the warp-per-stream decoder (warp_decode.cuh) ------------------------------------------
 DEFL_DEV bool     any(unsigned mask, bool p) { return __any_sync(mask, p); }

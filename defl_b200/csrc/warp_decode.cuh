@@ -47,7 +47,7 @@ struct WarpSmem {
   uint16_t dist[kDistTab];
   union {
     BuildScratch s;              // while a block header is parsed
-    uint8_t      stage[kStageV3];  // while tokens are resolved
+    uint16_t     stage[kStageV3];  // while tokens are resolved (bytes, or 16-bit symbols in split decode)
   };
 };
 static_assert(sizeof(WarpSmem) % 16 == 0, "WarpSmem alignment");
@@ -254,8 +254,12 @@ DEFL_DEV void lane_redo(const uint16_t* lit, const uint16_t* dist, const uint32_
 // toks[0..count) are consecutive tokens of the stream; the bytes they produce start at dst[P].
 // Checks what needs the absolute position (infl.c:816-821): distance > produced so far, output full.
 // Returns a Reason; P advances over everything produced before a failing token.
-DEFL_DEV uint32_t resolve_tokens(uint8_t* stage, int lane, const uint32_t* toks, uint32_t count, uint8_t* dst0,
-                                 uint32_t cap, uint32_t& P) {
+// SYM = uint8_t: plain bytes.  SYM = uint16_t (split decode of one large stream, split_decode.cuh): the
+// chunk does not know the 32 KiB before its start, so a byte copied from there becomes the marker
+// 0x8000 | k (k = index into that window) and markers are copied around like bytes; `hist` = 32768 then.
+template <typename SYM>
+DEFL_DEV uint32_t resolve_tokens(uint16_t* stage, int lane, const uint32_t* toks, uint32_t count, SYM* dst0,
+                                 uint32_t cap, uint32_t& P, uint32_t hist) {
   const unsigned le = simt::lanemask_le();
   uint32_t h = 0;
 #pragma unroll 1
@@ -272,7 +276,7 @@ DEFL_DEV uint32_t resolve_tokens(uint8_t* stage, int lane, const uint32_t* toks,
     }
     const uint32_t o = inc - olen;                         // this token's first byte inside the batch
     const uint32_t d1 = (tok >> 9) & 0x7FFFu;              // distance - 1
-    const bool bad_dist = (tok >> 31) && d1 >= P + o;
+    const bool bad_dist = (tok >> 31) && d1 >= P + o + hist;
     const bool bad_full = olen != 0u && inc > cap - P;
     const bool nofit    = inc > (uint32_t)kStageV3;
     // all three are monotone or first-hit: keep the tokens before the first stop
@@ -286,7 +290,7 @@ DEFL_DEV uint32_t resolve_tokens(uint8_t* stage, int lane, const uint32_t* toks,
     n = keep;
     if ((uint32_t)lane >= n) { tok = 0u; olen = 0u; }
     const uint32_t B = simt::shfl(kFull, inc, (int)n - 1);
-    uint8_t*       dst = dst0 + P;
+    SYM*           dst = dst0 + P;
 
     const bool dep = (tok >> 31) && (d1 + 1u < o + olen);
     if (dep) tok |= kTokIsDep;
@@ -316,7 +320,9 @@ DEFL_DEV uint32_t resolve_tokens(uint8_t* stage, int lane, const uint32_t* toks,
               val[u] = (t >> (8u * (j - oi))) & 255u;
               have[u] = true;
             } else if (!(t & kTokIsDep)) {
-              val[u] = simt::ld_out8(dst + j - (((t >> 9) & 0x7FFFu) + 1u));
+              const int32_t back = (int32_t)j - (int32_t)(((t >> 9) & 0x7FFFu) + 1u);
+              if (sizeof(SYM) == 2 && (int32_t)P + back < 0) val[u] = 0x8000u | (uint32_t)((int32_t)P + back + 32768);
+              else val[u] = simt::ld_out(dst + back);
               have[u] = true;
             }
           }
@@ -326,8 +332,8 @@ DEFL_DEV uint32_t resolve_tokens(uint8_t* stage, int lane, const uint32_t* toks,
       for (int u = 0; u < 4; u++) {
         const uint32_t j = base + 32u * (uint32_t)u + (uint32_t)lane;
         if (have[u]) {
-          stage[j] = (uint8_t)val[u];
-          dst[j] = (uint8_t)val[u];
+          stage[j] = (uint16_t)val[u];
+          dst[j] = (SYM)val[u];
         }
       }
     }
@@ -345,9 +351,12 @@ DEFL_DEV uint32_t resolve_tokens(uint8_t* stage, int lane, const uint32_t* toks,
       for (uint32_t r = (uint32_t)lane; r < len; r += 32u) {
         const uint32_t sr = dist < len ? r % dist : r;     // a period shorter than the match repeats
         const int32_t  so = (int32_t)oi - (int32_t)dist + (int32_t)sr;
-        const uint8_t  v  = so < 0 ? (uint8_t)simt::ld_out8(dst + so) : stage[so];
-        stage[oi + r] = v;
-        dst[oi + r] = v;
+        uint32_t v;
+        if (so >= 0) v = stage[so];
+        else if (sizeof(SYM) == 2 && (int32_t)P + so < 0) v = 0x8000u | (uint32_t)((int32_t)P + so + 32768);
+        else v = simt::ld_out(dst + so);
+        stage[oi + r] = (uint16_t)v;
+        dst[oi + r] = (SYM)v;
       }
     }
     simt::syncwarp(kFull);
@@ -375,9 +384,11 @@ DEFL_DEV WarpScratch scratch_of(void* base) {
 // Decode from absolute bit `cur` (a token boundary inside a Huffman block whose tables are in sm) as far
 // as one window reaches.  On return `cur` is where the stream goes on; the result is LS_OK (window done,
 // block goes on), LS_EOB (block ended at cur), or LS_FAIL | reason << 8.
+// COUNT: only add up what the window's tokens would produce (first pass of the split decode).
+template <typename SYM, bool COUNT>
 DEFL_DEV uint32_t decode_window(WarpSmem& sm, const WarpScratch& sc, int lane, const uint32_t* words,
-                                uint32_t wend, uint64_t end_bit, uint64_t& cur, uint8_t* dst, uint32_t cap,
-                                uint32_t& pos) {
+                                uint32_t wend, uint64_t end_bit, uint64_t& cur, SYM* dst, uint32_t cap,
+                                uint32_t& pos, uint32_t hist) {
   const uint32_t bw   = (uint32_t)(cur >> 5);
   const uint32_t rel0 = (uint32_t)(cur & 31u);
   const uint64_t left64 = end_bit - ((uint64_t)bw << 5);
@@ -418,14 +429,31 @@ DEFL_DEV uint32_t decode_window(WarpSmem& sm, const WarpScratch& sc, int lane, c
   simt::syncwarp(kFull);
 
   uint32_t reason = R_NONE;
+  if (COUNT) {
+    // every lane adds up its own true tokens
+    uint32_t bytes = 0;
+    if (lane <= last) {
+      for (uint32_t i = 0; i < tj.nf; i++) {
+        const uint32_t t = simt::ld_tok(fix + i);
+        bytes += (t >> 31) ? (t & 511u) : ((t >> 24) & 7u);
+      }
+      for (uint32_t i = tj.m; i < tj.n; i++) {
+        const uint32_t t = simt::ld_tok(seg + i);
+        bytes += (t >> 31) ? (t & 511u) : ((t >> 24) & 7u);
+      }
+    }
+    simt::syncwarp(kFull);
+    pos += simt::reduce_add(kFull, bytes);
+  } else {
 #pragma unroll 1
-  for (int L = 0; L <= last && reason == R_NONE; L++) {
-    const uint32_t nf = simt::shfl(kFull, tj.nf, L);
-    const uint32_t m  = simt::shfl(kFull, tj.m, L);
-    const uint32_t n  = simt::shfl(kFull, tj.n, L);
-    if (nf) reason = resolve_tokens(sm.stage, lane, sc.fix + (uint32_t)L * kFixCap, nf, dst, cap, pos);
-    if (reason == R_NONE && n > m)
-      reason = resolve_tokens(sm.stage, lane, sc.spec + (uint32_t)L * kSpecCap + m, n - m, dst, cap, pos);
+    for (int L = 0; L <= last && reason == R_NONE; L++) {
+      const uint32_t nf = simt::shfl(kFull, tj.nf, L);
+      const uint32_t m  = simt::shfl(kFull, tj.m, L);
+      const uint32_t n  = simt::shfl(kFull, tj.n, L);
+      if (nf) reason = resolve_tokens<SYM>(sm.stage, lane, sc.fix + (uint32_t)L * kFixCap, nf, dst, cap, pos, hist);
+      if (reason == R_NONE && n > m)
+        reason = resolve_tokens<SYM>(sm.stage, lane, sc.spec + (uint32_t)L * kSpecCap + m, n - m, dst, cap, pos, hist);
+    }
   }
   if (reason) return fail_stat(reason);
 
@@ -481,7 +509,7 @@ DEFL_DEV void inflate_stream_warp(WarpSmem& sm, const WarpScratch& sc, int lane,
       uint32_t st;
 #pragma unroll 1
       do {
-        st = decode_window(sm, sc, lane, br.w, br.wend, end_bit, cur, dst, cap, pos);
+        st = decode_window<uint8_t, false>(sm, sc, lane, br.w, br.wend, end_bit, cur, dst, cap, pos, 0u);
       } while (st == LS_OK);
       if (st != LS_EOB) { reason = st >> 8; break; }
       br.seek(cur);

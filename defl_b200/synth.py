@@ -158,3 +158,28 @@ def pack(blobs, align=16):
     for b, o in zip(blobs, offs):
         buf[o:o + len(b)] = np.frombuffer(b, dtype=np.uint8)
     return buf, offs, lens
+
+
+def single_stream(total_bytes, seed=0, level=6, stripe=1 << 20, slice_bytes=16 << 20, threads=None):
+    """BASELINE.json configs[3]: ONE zlib stream over `total_bytes` of text/log stripes.  Built pigz-style so the
+    host needs seconds, not minutes: slices are deflated in parallel as raw deflate ending in a full flush
+    (byte-aligned, non-final) and concatenated; the last slice ends the stream.  -> (raw, zlib stream)"""
+    threads = threads or min(32, os.cpu_count() or 1)
+    nstripes = (total_bytes + stripe - 1) // stripe
+
+    def stripe_bytes(i):
+        n = min(stripe, total_bytes - i * stripe)
+        return payload("text" if i % 2 == 0 else "log", n, seed * 100003 + i)
+
+    with ThreadPoolExecutor(threads) as ex:
+        raw = b"".join(ex.map(stripe_bytes, range(nstripes)))
+    nslices = max(1, (total_bytes + slice_bytes - 1) // slice_bytes)
+
+    def one(k):
+        c = zlib.compressobj(level, zlib.DEFLATED, -15, 8, zlib.Z_DEFAULT_STRATEGY)
+        part = raw[k * slice_bytes:(k + 1) * slice_bytes]
+        return c.compress(part) + c.flush(zlib.Z_FINISH if k == nslices - 1 else zlib.Z_FULL_FLUSH)
+
+    with ThreadPoolExecutor(threads) as ex:
+        body = b"".join(ex.map(one, range(nslices)))
+    return raw, b"\x78\x9c" + body + (zlib.adler32(raw) & 0xFFFFFFFF).to_bytes(4, "big")

@@ -185,3 +185,94 @@ extern "C" int emu_warp_inflate(const uint8_t* src, uint32_t srclen, uint8_t* ds
   free(sm); free(scratch);
   return out->code;
 }
+
+// ---- split decode of one stream (split_decode.cuh): chunks run one after another on one emulated warp ----
+#include "../../defl_b200/csrc/split_decode.cuh"
+namespace {
+
+struct ChunkJob {
+  simt::Group*        grp;
+  int                 lane;
+  defl::WarpSmem*     sm;
+  void*               scratch;
+  const uint8_t*      src;
+  uint32_t            srclen;
+  const uint64_t*     cand;
+  uint32_t            ncand, me;
+  uint16_t*           dst;
+  uint32_t            cap;
+  bool                count;
+  defl::SplitChunkOut* out;
+};
+
+void* chunk_main(void* arg) {
+  ChunkJob* j = static_cast<ChunkJob*>(arg);
+  simt::t_group = j->grp;
+  simt::t_lane  = j->lane;
+  defl::SplitChunkOut o;
+  const uint32_t hist = j->me == 0 ? 0u : 32768u;
+  if (j->count)
+    defl::inflate_chunk_warp<uint16_t, true>(*j->sm, defl::scratch_of(j->scratch), j->lane, j->src, j->srclen, j->cand,
+                                             j->ncand, j->me, nullptr, 0xFFFFFFFFu, hist, o);
+  else
+    defl::inflate_chunk_warp<uint16_t, false>(*j->sm, defl::scratch_of(j->scratch), j->lane, j->src, j->srclen, j->cand,
+                                              j->ncand, j->me, j->dst, j->cap, hist, o);
+  if (j->lane == 0) *j->out = o;
+  return nullptr;
+}
+
+void run_chunk(defl::WarpSmem* sm, void* scratch, const uint8_t* src, uint32_t srclen, const uint64_t* cand,
+               uint32_t ncand, uint32_t me, uint16_t* dst, uint32_t cap, bool count, defl::SplitChunkOut* out) {
+  simt::Group grp;
+  grp.G = 32;
+  pthread_barrier_init(&grp.bar, nullptr, 32);
+  std::vector<ChunkJob>  jobs(32);
+  std::vector<pthread_t> th(32);
+  for (int i = 0; i < 32; i++) jobs[i] = ChunkJob{&grp, i, sm, scratch, src, srclen, cand, ncand, me, dst, cap, count, out};
+  for (int i = 1; i < 32; i++) pthread_create(&th[i], nullptr, chunk_main, &jobs[i]);
+  chunk_main(&jobs[0]);
+  for (int i = 1; i < 32; i++) pthread_join(th[i], nullptr);
+  pthread_barrier_destroy(&grp.bar);
+}
+
+}  // namespace
+
+// cand[0] must be the first block of the stream.  Returns produced bytes, or -1 - (failing step).
+extern "C" long emu_split_inflate(const uint8_t* src, uint32_t srclen, const uint64_t* cand, uint32_t ncand,
+                                  uint8_t* dst, uint32_t cap, uint64_t* end_bit) {
+  defl::WarpSmem* sm = static_cast<defl::WarpSmem*>(aligned_alloc(64, (sizeof(defl::WarpSmem) + 63) & ~63ul));
+  void* scratch = aligned_alloc(64, defl::kWarpScratchBytes);
+  std::vector<defl::SplitChunkOut> outs(ncand);
+  for (uint32_t i = 0; i < ncand; i++) run_chunk(sm, scratch, src, srclen, cand, ncand, i, nullptr, 0, true, &outs[i]);
+  std::vector<uint32_t> chain;
+  std::vector<uint64_t> off;
+  uint64_t total = 0;
+  long rc = 0;
+  for (uint32_t i = 0;;) {
+    if ((outs[i].status & 0xFF) == defl::CH_FAIL) { rc = -1; break; }
+    chain.push_back(i); off.push_back(total); total += outs[i].out_bytes;
+    if (total > cap) { rc = -2; break; }
+    if (outs[i].status == defl::CH_FINAL) { *end_bit = outs[i].end_bit; break; }
+    if (outs[i].link <= i || outs[i].link >= ncand) { rc = -3; break; }
+    i = outs[i].link;
+  }
+  if (rc == 0) {
+    off.push_back(total);
+    std::vector<uint16_t> sym(total + 8, 0xFFFF);
+    for (size_t k = 0; k < chain.size() && rc == 0; k++) {
+      defl::SplitChunkOut o2;
+      run_chunk(sm, scratch, src, srclen, cand, ncand, chain[k], sym.data() + off[k], outs[chain[k]].out_bytes, false, &o2);
+      if (o2.status != outs[chain[k]].status || o2.out_bytes != outs[chain[k]].out_bytes) rc = -4;
+    }
+    if (rc == 0) {
+      uint32_t cc = 0;
+      for (uint64_t i = 0; i < total; i++) {
+        while (cc + 1 < chain.size() && off[cc + 1] <= i) cc++;
+        dst[i] = (uint8_t)defl::resolve_marker(sym.data(), off.data(), cc, i);
+      }
+      rc = (long)total;
+    }
+  }
+  free(sm); free(scratch);
+  return rc;
+}

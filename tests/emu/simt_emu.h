@@ -108,6 +108,8 @@ inline void backoff(unsigned) { sched_yield(); }
 inline uint32_t atomic_add_global(unsigned int* p, unsigned int v) { return __atomic_fetch_add(p, v, __ATOMIC_RELAXED); }
 inline long long ticks() { return 0; }
 inline uint32_t ld_out8(const uint8_t* p) { return *(const volatile uint8_t*)p; }
+inline uint32_t ld_out(const uint8_t* p) { return *(const volatile uint8_t*)p; }
+inline uint32_t ld_out(const uint16_t* p) { return *(const volatile uint16_t*)p; }
 inline bool any(unsigned mk, bool p) { return ballot(mk, p) != 0u; }
 inline int clz(uint32_t v) { return v ? __builtin_clz(v) : 32; }
 inline uint32_t reduce_add(unsigned, uint32_t v) {

@@ -114,6 +114,17 @@ def port_inflate(data, cap, flags=0):
     return rc, dst.raw[: res.outlen], res
 
 
+def port_block_index(data, flags=0, maxblocks=1 << 20):
+    """-> (bit offsets of the block headers counted from the deflate body, output offsets)"""
+    data = bytes(data)
+    bits = np.zeros(maxblocks, dtype=np.uint64)
+    outs = np.zeros(maxblocks, dtype=np.uint64)
+    src = _buf(data)
+    n = port().oracle_block_index(ctypes.addressof(src), len(data), flags, bits.ctypes.data, outs.ctypes.data, maxblocks)
+    assert n >= 0
+    return [int(b) for b in bits[:n]], [int(o) for o in outs[:n]]
+
+
 def port_inflate_chunks(chunks, cap, flags=0):
     data = b"".join(bytes(c) for c in chunks)
     offs = np.zeros(len(chunks) + 1, dtype=np.uint64)

@@ -162,3 +162,28 @@ def test_warp_large_streams_logic(emu):
             rc0, out0, r0 = ol.port_inflate(d, cap, 1)
             rc, out, o = run_warp(emu, d, cap, 1)
             assert rc == rc0 == -1, (k, cap)
+
+
+# ---- split decode of one large stream (defl_b200/csrc/split_decode.cuh): chunks, markers ---------------
+def test_split_chunks_and_markers_logic(emu):
+    """Chunks that start at true block boundaries (from the oracle's block index), decoded in isolation into
+    16-bit symbols with markers for the unknown window, then marker resolution: bytes equal the oracle's."""
+    from defl_b200 import synth
+    for kind, size, level in (("text", 700000, 6), ("log", 900000, 6), ("png", 400000, 1)):
+        raw, z = synth.make_streams([(kind, size, 21, level, zlib.Z_DEFAULT_STRATEGY)], threads=1)[0]
+        bits, outs_at = ol.port_block_index(z, 1)
+        assert len(bits) >= 6
+        # every other block start is a candidate (stream-relative bits: the index counts from the body)
+        cand = [bits[0] + 16] + [b + 16 for b in bits[2::2]]
+        arr = (ctypes.c_uint64 * len(cand))(*cand)
+        buf = ctypes.create_string_buffer(len(z) + 16)
+        base = ctypes.addressof(buf)
+        off = (-base) % 4
+        ctypes.memmove(base + off, z, len(z))
+        dst = ctypes.create_string_buffer(len(raw) + 16)
+        end_bit = ctypes.c_uint64(0)
+        emu.emu_split_inflate.restype = ctypes.c_long
+        n = emu.emu_split_inflate(ctypes.c_void_p(base + off), len(z), arr, len(cand), dst, len(raw), ctypes.byref(end_bit))
+        assert n == len(raw), (kind, n)
+        assert dst.raw[:n] == raw, kind
+        assert (end_bit.value + 7) // 8 == len(z) - 4

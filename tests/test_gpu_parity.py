@@ -312,3 +312,52 @@ def test_pipeline_shapes(gpu_lib):
     finally:
         d.set_pipeline_shape(0)
         d.set_engine(3)
+
+
+def test_split_single_large_stream(gpu_lib):
+    """BASELINE.json configs[3] at reduced size: one large stream decoded by many warps from speculative block
+    starts (split_decode.cuh).  Bytes, lengths and Adler-32 equal the oracle's; streams the block search cannot
+    split (stored-only, fixed-Huffman) and damaged streams come out of the one-warp decoder with the oracle's code."""
+    import torch
+    from defl_b200 import synth
+    d = gpu_lib
+    raw, z = synth.single_stream(40 << 20, seed=3, slice_bytes=8 << 20)
+    assert zlib.decompress(z) == raw
+    # host pointers
+    res, outs = d.infl_buf_batch([z], [len(raw)], d.INFL_ZLIB | d.INFL_BATCH_VERIFY_ADLER)
+    g = res[0]
+    assert int(g["code"]) == 0 and int(g["info"]) & 4, (int(g["code"]), int(g["info"]))
+    assert bytes(outs[0]) == raw
+    assert int(g["outlen"]) == len(raw) and int(g["inpos"]) == len(z) - 4
+    assert int(g["adler"]) == int(g["adler_stored"]) == (zlib.adler32(raw) & 0xFFFFFFFF)
+    # one continuous deflate history (no flush points), other payloads, with a stored stretch in the middle
+    parts = [synth.payload("text", 9 << 20, 1), synth.payload("rand", 1 << 20, 2), synth.payload("png", 6 << 20, 3),
+             synth.payload("log", 8 << 20, 4)]
+    raw2 = b"".join(parts)
+    z2 = zlib.compress(raw2, 6)
+    code, want, r = ol.port_inflate(z2, len(raw2), 1)
+    assert code == 0 and want == raw2
+    res, outs = d.infl_buf_batch([z2, z], [len(raw2), len(raw)], d.INFL_ZLIB)
+    assert int(res[0]["code"]) == 0 and int(res[0]["info"]) & 4
+    assert bytes(outs[0]) == raw2 and bytes(outs[1]) == raw
+    assert int(res[0]["adler"]) == r.adler and int(res[0]["inpos"]) == r.inpos
+    # the same stream with splitting switched off: identical result record
+    res1, outs1 = d.infl_buf_batch([z2], [len(raw2)], d.INFL_ZLIB | d.INFL_BATCH_NO_SPLIT)
+    assert bytes(outs1[0]) == raw2 and not (int(res1[0]["info"]) & 4)
+    for f in ("code", "adler", "outlen", "inpos", "adler_stored"):
+        assert int(res1[0][f]) == int(res[0][f]), f
+    # cannot be split: stored only / fixed Huffman; damaged: truncated, one byte short of output, flipped bit
+    rnd = synth.payload("rand", 6 << 20, 9)
+    c = zlib.compressobj(6, zlib.DEFLATED, 15, 8, zlib.Z_FIXED)
+    txt = synth.payload("text", 12 << 20, 5)
+    zfix = c.compress(txt) + c.flush()
+    bad = bytearray(z2)
+    bad[len(bad) // 2] ^= 0x10
+    cases = [(zlib.compress(rnd, 6), len(rnd)), (zfix, len(txt)), (z2[: len(z2) * 3 // 4], len(raw2)),
+             (z2, len(raw2) - 1), (bytes(bad), len(raw2))]
+    res, outs = d.infl_buf_batch([c_[0] for c_ in cases], [c_[1] for c_ in cases], d.INFL_ZLIB)
+    for (data, cap), g, out in zip(cases, res, outs):
+        code, want, r = ol.port_inflate(data, cap, 1)
+        assert int(g["code"]) == code
+        if code == 0:
+            assert bytes(out) == want and int(g["adler"]) == r.adler
