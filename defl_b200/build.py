@@ -7,8 +7,8 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libdefl_b200.so")
 SOURCES = ["defl_b200.cu"]
-DEPS = ["defl_b200.cu", "kernels.cuh", "inflate_core.cuh", "simt_cuda.cuh", "pipeline.cuh", "split_decode.cuh",
-        "../../include/defl/infl.h", "../../include/defl/infl_batch.h", "../../include/defl/common.h"]
+DEPS = sorted(f for f in os.listdir(CSRC) if f.endswith((".cu", ".cuh"))) + \
+       ["../../include/defl/infl.h", "../../include/defl/infl_batch.h", "../../include/defl/common.h"]
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",

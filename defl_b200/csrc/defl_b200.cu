@@ -9,6 +9,7 @@
 
 #include <algorithm>
 #include <atomic>
+#include <chrono>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -269,11 +270,16 @@ inline size_t align_up(size_t v) { return (v + kAlign - 1) & ~(kAlign - 1); }
 
 // ---- one large stream, decoded by the whole GPU (split_decode.cuh) ----------------------------------------------
 constexpr uint64_t kSplitMinBytes = 4ull << 20;      // compressed size from which a stream is worth splitting
-constexpr uint64_t kSplitMinGap   = 40960ull * 8;    // bits between chosen block starts: chunks produce >= 32 KiB
+uint32_t env_u32(const char* name, uint32_t dflt, uint32_t lo, uint32_t hi) {
+  const char* v = std::getenv(name);
+  if (!v || !*v) return dflt;
+  const unsigned long long x = std::strtoull(v, nullptr, 0);
+  return (uint32_t)std::min<unsigned long long>(hi, std::max<unsigned long long>(lo, x));
+}
 std::atomic<uint64_t> g_split_decodes{0};
 
 struct SplitBufs {
-  DevBuf d_found, d_cand, d_jobs, d_outs, d_sym, d_off, d_partial;
+  DevBuf d_found, d_cand, d_jobs, d_outs, d_outs2, d_sym, d_off, d_partial, d_wbuf, d_tok;
 };
 SplitBufs g_split[kMaxDevices];
 
@@ -285,6 +291,17 @@ int split_decode_device(Engine* E, const uint8_t* d_src, uint64_t srclen, uint8_
   using namespace defl;
   SplitBufs& SB = g_split[E->dev];
   const bool zlib = (flags & 0xFF) == INFL_ZLIB;
+  // DEFL_SPLIT_TRACE=1: per-phase wall times on stderr (adds a stream synchronise per phase)
+  static const bool trace = std::getenv("DEFL_SPLIT_TRACE") != nullptr;
+  auto tnow = [] { return std::chrono::steady_clock::now(); };
+  auto tprev = tnow();
+  auto mark = [&](const char* what) {
+    if (!trace) return;
+    cudaStreamSynchronize(st);
+    const auto t = tnow();
+    std::fprintf(stderr, "[split] %-28s %8.3f ms\n", what, std::chrono::duration<double, std::milli>(t - tprev).count());
+    tprev = t;
+  };
   uint32_t   body = 0;
   if (zlib) {
     uint8_t h2[2];
@@ -300,35 +317,44 @@ int split_decode_device(Engine* E, const uint8_t* d_src, uint64_t srclen, uint8_
   const size_t smem = sizeof(WarpSmem) * kWarpsPerCta;
 
   // ---- F: block starts
-  const uint32_t ngran = (uint32_t)((srclen - body + kGranuleBytes - 1) / kGranuleBytes);
+  static const uint32_t granule = env_u32("DEFL_SPLIT_GRANULE", 32768u, 4096u, 1u << 24);
+  static const uint64_t min_gap = (uint64_t)env_u32("DEFL_SPLIT_GAP", 40960u, 0u, 1u << 28) * 8u;   // bits
+  const uint32_t ngran = (uint32_t)((srclen - body + granule - 1) / granule);
   if (SB.d_found.reserve((size_t)ngran * 8)) return UNZ_ERR;
-  {
-    auto kern = find_block_starts_kernel<kWarpsPerCta>;
-    static bool attr_done[kMaxDevices] = {false};
-    if (!attr_done[E->dev]) {
-      CU_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem), "cudaFuncSetAttribute");
-      attr_done[E->dev] = true;
-    }
-    kern<<<(ngran + kWarpsPerCta - 1) / kWarpsPerCta, kWarpsPerCta * 32, smem, st>>>(
-        d_src, (uint32_t)srclen, body, ngran, static_cast<uint64_t*>(SB.d_found.p));
-    CU_TRY(cudaGetLastError(), "find_block_starts_kernel launch");
-    g_launches.fetch_add(1, std::memory_order_relaxed);
-  }
+  find_block_starts_kernel<kWarpsPerCta><<<(ngran + kWarpsPerCta - 1) / kWarpsPerCta, kWarpsPerCta * 32, 0, st>>>(
+      d_src, (uint32_t)srclen, body, ngran, granule, static_cast<uint64_t*>(SB.d_found.p));
+  CU_TRY(cudaGetLastError(), "find_block_starts_kernel launch");
+  g_launches.fetch_add(1, std::memory_order_relaxed);
   std::vector<uint64_t> found(ngran);
   CU_TRY(cudaMemcpyAsync(found.data(), SB.d_found.p, (size_t)ngran * 8, cudaMemcpyDeviceToHost, st), "D2H block starts");
   CU_TRY(cudaStreamSynchronize(st), "find_block_starts_kernel");
+  mark("F find_block_starts");
   std::vector<uint64_t> cand;
   cand.push_back((uint64_t)body * 8);
   for (uint64_t f : found)
-    if (f != kNoCandidate && f >= cand.back() + kSplitMinGap) cand.push_back(f);
+    if (f != kNoCandidate && f >= cand.back() + min_gap && f > cand.back()) cand.push_back(f);
   const uint32_t ncand = (uint32_t)cand.size();
   if (ncand < 8) return UNZ_NOOP;
 
   // ---- A: every candidate counts its chunk
+  // The count pass keeps each chunk's tokens (tok_per_byte tokens of budget per compressed byte, regions
+  // laid out by compressed position) so that the decode pass only has to turn them into bytes.
+  static const uint32_t tok_per_byte = env_u32("DEFL_SPLIT_TOKENS_PER_BYTE", 2u, 0u, 32u);
+  uint32_t* d_tok = nullptr;
+  if (tok_per_byte) {
+    if (SB.d_tok.reserve_exact((size_t)tok_per_byte * srclen * 4 + 64) == UNZ_OK) d_tok = static_cast<uint32_t*>(SB.d_tok.p);
+    else cudaGetLastError();       // no room for it: the decode pass decodes again, as before
+  }
   std::vector<SplitJob> jobs(ncand);
-  for (uint32_t i = 0; i < ncand; i++) { jobs[i].cand = i; jobs[i].cap = 0; jobs[i].out_off = 0; }
+  for (uint32_t i = 0; i < ncand; i++) {
+    const uint64_t b0 = cand[i] >> 3, b1 = i + 1 < ncand ? cand[i + 1] >> 3 : srclen;
+    jobs[i].cand = i; jobs[i].cap = 0; jobs[i].out_off = 0;
+    jobs[i].tok_off = (uint64_t)tok_per_byte * b0;
+    jobs[i].tok_cap = (uint32_t)std::min<uint64_t>((uint64_t)tok_per_byte * (b1 - b0), 0xFFFFFFF0ull);
+    jobs[i].ntok = kNoTokens;
+  }
   if (SB.d_cand.reserve((size_t)ncand * 8) || SB.d_jobs.reserve((size_t)ncand * sizeof(SplitJob)) ||
-      SB.d_outs.reserve((size_t)ncand * sizeof(SplitChunkOut)))
+      SB.d_outs.reserve((size_t)ncand * sizeof(SplitChunkOut)) || SB.d_outs2.reserve((size_t)ncand * sizeof(SplitChunkOut)))
     return UNZ_ERR;
   CU_TRY(cudaMemcpyAsync(SB.d_cand.p, cand.data(), (size_t)ncand * 8, cudaMemcpyHostToDevice, st), "H2D candidates");
   CU_TRY(cudaMemcpyAsync(SB.d_jobs.p, jobs.data(), (size_t)ncand * sizeof(SplitJob), cudaMemcpyHostToDevice, st), "H2D jobs");
@@ -344,11 +370,11 @@ int split_decode_device(Engine* E, const uint8_t* d_src, uint64_t srclen, uint8_
     if (count)
       split_chunk_kernel<true, kWarpsPerCta><<<grid, kWarpsPerCta * 32, smem, st>>>(
           d_src, (uint32_t)srclen, static_cast<uint64_t*>(SB.d_cand.p), ncand, static_cast<SplitJob*>(SB.d_jobs.p), njobs,
-          sym, static_cast<SplitChunkOut*>(SB.d_outs.p), ticket, scratch);
+          sym, static_cast<SplitChunkOut*>(SB.d_outs.p), ticket, scratch, d_tok);
     else
       split_chunk_kernel<false, kWarpsPerCta><<<grid, kWarpsPerCta * 32, smem, st>>>(
           d_src, (uint32_t)srclen, static_cast<uint64_t*>(SB.d_cand.p), ncand, static_cast<SplitJob*>(SB.d_jobs.p), njobs,
-          sym, static_cast<SplitChunkOut*>(SB.d_outs.p), ticket, scratch);
+          sym, static_cast<SplitChunkOut*>(SB.d_outs2.p), ticket, scratch, d_tok);
     CU_TRY(cudaGetLastError(), "split_chunk_kernel launch");
     g_launches.fetch_add(1, std::memory_order_relaxed);
     return UNZ_OK;
@@ -357,6 +383,7 @@ int split_decode_device(Engine* E, const uint8_t* d_src, uint64_t srclen, uint8_
   std::vector<SplitChunkOut> outs(ncand);
   CU_TRY(cudaMemcpyAsync(outs.data(), SB.d_outs.p, (size_t)ncand * sizeof(SplitChunkOut), cudaMemcpyDeviceToHost, st), "D2H chunk sizes");
   CU_TRY(cudaStreamSynchronize(st), "split_chunk_kernel (count)");
+  mark("A count pass");
 
   // ---- the chain of true chunks, from the stream's first block to its final block
   std::vector<uint32_t> chain;
@@ -375,25 +402,45 @@ int split_decode_device(Engine* E, const uint8_t* d_src, uint64_t srclen, uint8_
   }
   off.push_back(total);
   const uint32_t nchunk = (uint32_t)chain.size();
+  if (nchunk > 1 && off[1] < kWinBytes) return UNZ_NOOP;   // markers index the 32 KiB before a chunk: they must exist
 
   // ---- C: the chain decodes into 16-bit symbols at final offsets
-  for (uint32_t k = 0; k < nchunk; k++) {
-    jobs[k].cand = chain[k]; jobs[k].cap = outs[chain[k]].out_bytes; jobs[k].out_off = off[k];
+  // largest chunk first: the pass ends when its slowest warp does
+  std::vector<uint32_t> perm(nchunk);
+  std::iota(perm.begin(), perm.end(), 0u);
+  std::stable_sort(perm.begin(), perm.end(),
+                   [&](uint32_t a, uint32_t b) { return outs[chain[a]].out_bytes > outs[chain[b]].out_bytes; });
+  for (uint32_t j = 0; j < nchunk; j++) {
+    const uint32_t k = perm[j];
+    jobs[j].cand = chain[k]; jobs[j].cap = outs[chain[k]].out_bytes; jobs[j].out_off = off[k];
+    jobs[j].tok_off = (uint64_t)tok_per_byte * (cand[chain[k]] >> 3);
+    jobs[j].tok_cap = 0;
+    jobs[j].ntok = d_tok ? outs[chain[k]].ntok : kNoTokens;
   }
   if (SB.d_sym.reserve((size_t)total * 2 + 64) || SB.d_off.reserve((size_t)(nchunk + 1) * 8)) return UNZ_ERR;
   CU_TRY(cudaMemcpyAsync(SB.d_jobs.p, jobs.data(), (size_t)nchunk * sizeof(SplitJob), cudaMemcpyHostToDevice, st), "H2D jobs");
   CU_TRY(cudaMemcpyAsync(SB.d_off.p, off.data(), (size_t)(nchunk + 1) * 8, cudaMemcpyHostToDevice, st), "H2D offsets");
   if (launch_chunks(false, nchunk, static_cast<uint16_t*>(SB.d_sym.p)) != UNZ_OK) return UNZ_ERR;
+  mark("C decode pass");
+  if (trace) std::fprintf(stderr, "[split] ncand %u nchunk %u total %llu\n", ncand, nchunk, (unsigned long long)total);
   std::vector<SplitChunkOut> outs2(nchunk);
-  CU_TRY(cudaMemcpyAsync(outs2.data(), SB.d_outs.p, (size_t)nchunk * sizeof(SplitChunkOut), cudaMemcpyDeviceToHost, st), "D2H chunk results");
+  CU_TRY(cudaMemcpyAsync(outs2.data(), SB.d_outs2.p, (size_t)nchunk * sizeof(SplitChunkOut), cudaMemcpyDeviceToHost, st), "D2H chunk results");
 
   // ---- D: markers -> bytes, Adler-32
-  const uint32_t nblk = (uint32_t)((total + 4095) / 4096);
+  const uint32_t nblk = (uint32_t)((total + defl::kResolvePerBlock - 1) / defl::kResolvePerBlock);
   std::vector<uint32_t> partial((size_t)nblk * 2);
   if (nblk) {
     if (SB.d_partial.reserve((size_t)nblk * 8)) return UNZ_ERR;
+    if (nchunk > 1) {
+      if (SB.d_wbuf.reserve((size_t)(nchunk - 1) * kWinBytes)) return UNZ_ERR;
+      window_resolve_kernel<<<(nchunk - 1) * 16u, 256, 0, st>>>(static_cast<uint16_t*>(SB.d_sym.p), static_cast<uint64_t*>(SB.d_off.p),
+                                                                nchunk, static_cast<uint8_t*>(SB.d_wbuf.p));
+      CU_TRY(cudaGetLastError(), "window_resolve_kernel launch");
+      g_launches.fetch_add(1, std::memory_order_relaxed);
+    }
     marker_resolve_kernel<<<nblk, 256, 0, st>>>(static_cast<uint16_t*>(SB.d_sym.p), static_cast<uint64_t*>(SB.d_off.p), nchunk,
-                                                 d_dst, total, static_cast<uint32_t*>(SB.d_partial.p));
+                                                 static_cast<uint8_t*>(SB.d_wbuf.p), d_dst, total,
+                                                 static_cast<uint32_t*>(SB.d_partial.p));
     CU_TRY(cudaGetLastError(), "marker_resolve_kernel launch");
     g_launches.fetch_add(1, std::memory_order_relaxed);
     CU_TRY(cudaMemcpyAsync(partial.data(), SB.d_partial.p, (size_t)nblk * 8, cudaMemcpyDeviceToHost, st), "D2H adler partials");
@@ -403,10 +450,15 @@ int split_decode_device(Engine* E, const uint8_t* d_src, uint64_t srclen, uint8_
   const bool has_trailer = zlib && srclen - inpos >= 4;
   if (has_trailer) CU_TRY(cudaMemcpyAsync(trailer, d_src + inpos, 4, cudaMemcpyDeviceToHost, st), "D2H trailer");
   CU_TRY(cudaStreamSynchronize(st), "split decode");
-  for (uint32_t k = 0; k < nchunk; k++)
-    if (outs2[k].status != outs[chain[k]].status || outs2[k].out_bytes != outs[chain[k]].out_bytes ||
-        outs2[k].end_bit != outs[chain[k]].end_bit)
+  mark("D marker resolve + adler");
+  for (uint32_t j = 0; j < nchunk; j++) {
+    const SplitChunkOut& a = outs[chain[perm[j]]];
+    const bool same = outs2[j].status == CH_REPLAYED
+                          ? outs2[j].out_bytes == a.out_bytes
+                          : (outs2[j].status == a.status && outs2[j].out_bytes == a.out_bytes && outs2[j].end_bit == a.end_bit);
+    if (!same)
       return UNZ_NOOP;            // cannot happen for a deterministic decode; the one-warp decoder has the last word
+  }
 
   uint64_t sa = 0, sw = 0;
   for (uint32_t b = 0; b < nblk; b++) { sa += partial[2 * b]; sw += partial[2 * b + 1]; }

@@ -23,20 +23,24 @@
 
 namespace defl {
 
-enum : uint32_t { CH_LINKED = 0, CH_FINAL = 1, CH_FAIL = 2 };   // CH_FAIL | reason << 8
+enum : uint32_t { CH_LINKED = 0, CH_FINAL = 1, CH_FAIL = 2, CH_REPLAYED = 3 };   // CH_FAIL | reason << 8
+constexpr uint32_t kNoTokens = 0xFFFFFFFFu;
 
 struct SplitChunkOut {
   uint64_t end_bit;     // stream-relative bit where the chunk stopped (a block boundary unless it failed)
   uint32_t status;      // CH_*
   uint32_t link;        // CH_LINKED: index of the candidate at end_bit
   uint32_t out_bytes;   // bytes the chunk produces
-  uint32_t pad;
+  uint32_t ntok;        // COUNT: tokens kept for the DECODE pass, or kNoTokens
 };
 
 struct SplitJob {
   uint32_t cand;        // index into cand[]: where the chunk starts
   uint32_t cap;         // DECODE: exactly the bytes the COUNT pass reported
   uint64_t out_off;     // DECODE: offset of the chunk's first symbol
+  uint64_t tok_off;     // where the chunk's tokens are kept (COUNT writes, DECODE reads)
+  uint32_t tok_cap;     // COUNT: token budget
+  uint32_t ntok;        // DECODE: tokens to replay, or kNoTokens = decode again
 };
 
 // stored block inside a chunk (infl_ft_stored, infl.c:659-715): count it, or copy it as symbols
@@ -66,7 +70,17 @@ DEFL_DEV uint32_t stored_block_sym(int lane, BitReader& br, const uint8_t* src, 
 template <typename SYM, bool COUNT>
 DEFL_DEV void inflate_chunk_warp(WarpSmem& sm, const WarpScratch& sc, int lane, const uint8_t* src, uint32_t srclen,
                                  const uint64_t* cand, uint32_t ncand, uint32_t me, SYM* dst, uint32_t cap,
-                                 uint32_t hist, SplitChunkOut& out) {
+                                 uint32_t hist, SplitChunkOut& out, TokSink* sink = nullptr,
+                                 const uint32_t* saved = nullptr, uint32_t nsaved = kNoTokens) {
+  if (!COUNT && saved && nsaved != kNoTokens) {
+    // the COUNT pass kept this chunk's tokens: only the byte-producing half of the work is left
+    uint32_t p = 0;
+    simt::syncwarp(kFull);
+    const uint32_t r = resolve_tokens<SYM>(sm.stage, lane, saved, nsaved, dst, cap, p, hist);
+    out.end_bit = 0; out.link = 0; out.ntok = nsaved; out.out_bytes = p;
+    out.status = r ? (CH_FAIL | (r << 8)) : (uint32_t)CH_REPLAYED;
+    return;
+  }
   Lane<32> L;
   L.gmask = kFull; L.lane = lane; L.wlane = lane;
   const uint32_t mis      = (uint32_t)((uintptr_t)src & 3u);
@@ -92,6 +106,7 @@ DEFL_DEV void inflate_chunk_warp(WarpSmem& sm, const WarpScratch& sc, int lane, 
     const uint32_t bfinal = hdr & 1u, btype = (hdr >> 1) & 3u;
     br.skip(3); br.norm();
     if (btype == 0) {
+      if (sink) sink->ok = false;          // stored bytes are not tokens: such a chunk decodes again
       reason = stored_block_sym<SYM, COUNT>(lane, br, src, srclen, base_bit, dst, pos, cap);
       if (reason) break;
     } else if (btype == 3) {
@@ -106,7 +121,7 @@ DEFL_DEV void inflate_chunk_warp(WarpSmem& sm, const WarpScratch& sc, int lane, 
       uint32_t st;
 #pragma unroll 1
       do {
-        st = decode_window<SYM, COUNT>(sm, sc, lane, br.w, br.wend, end_bit, cur, dst, cap, pos, hist);
+        st = decode_window<SYM, COUNT>(sm, sc, lane, br.w, br.wend, end_bit, cur, dst, cap, pos, hist, sink);
       } while (st == LS_OK);
       if (st != LS_EOB) { reason = st >> 8; break; }
       br.seek(cur);
@@ -117,7 +132,7 @@ DEFL_DEV void inflate_chunk_warp(WarpSmem& sm, const WarpScratch& sc, int lane, 
   out.status    = reason ? (CH_FAIL | (reason << 8)) : status;
   out.link      = next;
   out.out_bytes = pos;
-  out.pad       = 0;
+  out.ntok      = (COUNT && sink && sink->buf && sink->ok) ? sink->n : kNoTokens;
 }
 
 #ifdef __CUDACC__
@@ -126,7 +141,7 @@ __global__ void __launch_bounds__(WARPS * 32, 32 / WARPS)
 split_chunk_kernel(const uint8_t* __restrict__ src, uint32_t srclen, const uint64_t* __restrict__ cand,
                    uint32_t ncand, const SplitJob* __restrict__ jobs, uint32_t njobs, uint16_t* __restrict__ sym,
                    SplitChunkOut* __restrict__ outs, unsigned int* __restrict__ ticket,
-                   unsigned char* __restrict__ scratch) {
+                   unsigned char* __restrict__ scratch, uint32_t* __restrict__ tokbuf) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   WarpSmem&         sm = reinterpret_cast<WarpSmem*>(smem_raw)[warp];
@@ -138,10 +153,14 @@ split_chunk_kernel(const uint8_t* __restrict__ src, uint32_t srclen, const uint6
     if (k >= njobs) break;
     const SplitJob job = jobs[k];
     SplitChunkOut  o;
+    TokSink        sink;
+    sink.buf = (COUNT && tokbuf) ? tokbuf + job.tok_off : nullptr;
+    sink.cap = job.tok_cap; sink.n = 0; sink.ok = sink.buf != nullptr;
     // the chunk that starts the stream has no unknown window before it
     inflate_chunk_warp<uint16_t, COUNT>(sm, sc, lane, src, srclen, cand, ncand, job.cand,
                                         COUNT ? nullptr : sym + job.out_off, COUNT ? 0xFFFFFFFFu : job.cap,
-                                        job.cand == 0u ? 0u : 32768u, o);
+                                        job.cand == 0u ? 0u : 32768u, o, COUNT ? &sink : nullptr,
+                                        (!COUNT && tokbuf) ? tokbuf + job.tok_off : nullptr, job.ntok);
     if (lane == 0) outs[k] = o;
     simt::syncwarp(kFull);
   }
@@ -150,89 +169,234 @@ split_chunk_kernel(const uint8_t* __restrict__ src, uint32_t srclen, const uint6
 #endif  // __CUDACC__
 
 // ---- F: block-start search -------------------------------------------------------------------------------
-constexpr uint32_t kGranuleBytes = 32768;             // one search result per this much input
-constexpr uint64_t kNoCandidate  = ~0ull;
+constexpr uint64_t kNoCandidate = ~0ull;
 
-// Cheap per-position filters, one bit position per lane: a non-reserved dynamic header whose
-// code-length code is Kraft-complete (what every deflate encoder emits).  x0/x1/x2 = the 96 bits at p.
-DEFL_DEV bool header_plausible(uint32_t x0, uint32_t x1, uint32_t x2) {
-  if (((x0 >> 1) & 3u) != 2u) return false;                       // BTYPE = dynamic
-  if (((x0 >> 3) & 31u) > 29u || ((x0 >> 8) & 31u) > 29u) return false;   // HLIT <= 286, HDIST <= 30
-  const uint32_t n = ((x0 >> 13) & 15u) + 4u;
-  uint64_t y = (uint64_t)(x0 >> 17) | ((uint64_t)x1 << 15) | ((uint64_t)x2 << 47);
-  uint32_t kraft = 0;
-#pragma unroll 1
-  for (uint32_t i = 0; i < n; i++) {
-    const uint32_t l = (uint32_t)y & 7u;
-    y >>= 3;
-    kraft += l ? (128u >> l) : 0u;
-  }
-  return kraft == 128u;
+// The search is a funnel, every stage lane-parallel over bit positions (nothing here is warp-serial):
+//   1. cheap   : BTYPE = dynamic, HLIT <= 286, HDIST <= 30                       (22 % of positions pass)
+//   2. precode : the code-length code is Kraft-complete (what every encoder emits) (0.09 % pass), on a
+//                compacted list so that all 32 lanes work; 3 lengths per lookup in a 512-entry table
+//   3. header  : the lane decodes the whole code-length sequence in registers (canonical decode by
+//                comparisons, no table) and keeps Kraft sums: literal/length code complete, an end-of-block
+//                code, a non-empty distance code that is not over-subscribed.  32 candidates per round.
+// The first position of the granule that passes all three goes to found[g].
+#ifdef __CUDACC__
+DEFL_DEV bool header_cheap(uint32_t x0) {
+  return ((x0 >> 1) & 3u) == 2u && ((x0 >> 3) & 31u) <= 29u && ((x0 >> 8) & 31u) <= 29u;
 }
 
-// One warp per granule [g * 32 KiB, (g + 1) * 32 KiB) of the stream body: the first position that passes
-// the filters AND parses as a whole dynamic header with complete literal/length code, an end-of-block
-// code and a non-empty distance code goes to found[g].
-#ifdef __CUDACC__
+// x0/x1/x2 = the 96 bits at the candidate; kraft9[v] = sum over the three 3-bit lengths in v of (l ? 128 >> l : 0)
+DEFL_DEV bool precode_complete(uint32_t x0, uint32_t x1, uint32_t x2, const uint8_t* kraft9) {
+  const uint32_t nb = (((x0 >> 13) & 15u) + 4u) * 3u;              // 12..57 bits of lengths from bit 17 on
+  uint32_t f0 = simt::funnel_r(x0, x1, 17u) & 0x7FFFFFFu;          // lengths 0..8
+  uint32_t f1 = simt::funnel_r(x1, x2, 12u) & 0x7FFFFFFu;          // lengths 9..17
+  uint32_t f2 = (x2 >> 7) & 7u;                                    // length 18
+  if (nb < 27u) f0 &= (1u << nb) - 1u;
+  f1 = nb <= 27u ? 0u : (nb < 54u ? f1 & ((1u << (nb - 27u)) - 1u) : f1);
+  f2 = nb > 54u ? f2 : 0u;
+  const uint32_t k = kraft9[f0 & 511u] + kraft9[(f0 >> 9) & 511u] + kraft9[f0 >> 18] +
+                     kraft9[f1 & 511u] + kraft9[(f1 >> 9) & 511u] + kraft9[f1 >> 18] + kraft9[f2];
+  return k == 128u;
+}
+
+struct LaneBits {        // one lane's private bit reader over the input words
+  const uint32_t* w;
+  uint32_t        wend, widx, nb;
+  uint64_t        bb;
+  DEFL_DEV uint32_t ld(uint32_t i) const { return i < wend ? simt::ld_in32(w + i) : 0u; }
+  DEFL_DEV void init(const uint32_t* words, uint32_t we, uint64_t bit) {
+    w = words; wend = we;
+    widx = (uint32_t)(bit >> 5);
+    const uint32_t sh = (uint32_t)(bit & 31u);
+    bb = (((uint64_t)ld(widx + 1) << 32) | ld(widx)) >> sh;
+    nb = 64u - sh;
+    widx += 2;
+  }
+  DEFL_DEV uint32_t peek() const { return (uint32_t)bb; }
+  DEFL_DEV void skip(uint32_t n) {       // n <= 17
+    bb >>= n; nb -= n;
+    if (nb <= 32u) { bb |= (uint64_t)ld(widx++) << nb; nb += 32u; }
+  }
+};
+
+// Stage 3 for one lane: pc = absolute bit of the 3-bit block header.  The precode is known to be complete.
+DEFL_DEV bool header_full_check(const uint32_t* words, uint32_t wend, uint64_t pc, uint64_t end_bit) {
+  LaneBits br;
+  br.init(words, wend, pc);
+  uint32_t v = br.peek();
+  const uint32_t hlit = ((v >> 3) & 31u) + 257u, hdist = ((v >> 8) & 31u) + 1u, hclen = ((v >> 13) & 15u) + 4u;
+  const uint32_t n = hlit + hdist;
+  br.skip(17);
+  uint64_t used = 17u + 3u * hclen;
+  // the 19 code-length-code lengths, packed 3 bits each in symbol order (RFC 1951 3.2.7 permutation)
+  uint64_t clpack = 0;
+#pragma unroll 1
+  for (uint32_t i = 0; i < hclen; i++) {
+    clpack |= (uint64_t)(br.peek() & 7u) << (3u * cl_order(i));
+    br.skip(3);
+  }
+  // canonical code in a 7-bit MSB-aligned code space: lim(l) = upper end of the codes of length <= l
+  uint64_t cnt = 0;                        // byte l = symbols of length l
+#pragma unroll 1
+  for (uint32_t s = 0; s < 19u; s++) cnt += 1ull << (8u * ((uint32_t)(clpack >> (3u * s)) & 7u));
+  uint64_t lims = 0, offs = 0;             // byte l = lim(l) / number of coded symbols shorter than l
+  {
+    uint32_t acc = 0, o = 0;
+#pragma unroll
+    for (uint32_t l = 1; l <= 7u; l++) {
+      const uint32_t c = (uint32_t)(cnt >> (8u * l)) & 255u;
+      offs |= (uint64_t)o << (8u * l);
+      acc += c << (7u - l);
+      o += c;
+      lims |= (uint64_t)(acc > 255u ? 255u : acc) << (8u * l);
+    }
+  }
+  uint64_t slo = 0, shi = 0;               // symbols sorted by (length, symbol), 5 bits each, 12 per word
+  {
+    uint64_t cursor = offs;
+#pragma unroll 1
+    for (uint32_t s = 0; s < 19u; s++) {
+      const uint32_t l = (uint32_t)(clpack >> (3u * s)) & 7u;
+      if (l) {
+        const uint32_t pos = (uint32_t)(cursor >> (8u * l)) & 255u;
+        cursor += 1ull << (8u * l);
+        if (pos < 12u) slo |= (uint64_t)s << (5u * pos);
+        else shi |= (uint64_t)s << (5u * (pos - 12u));
+      }
+    }
+  }
+  const uint32_t limA = (uint32_t)(lims >> 8);                       // lim(1..4)
+  const uint32_t limB = ((uint32_t)(lims >> 40) & 0xFFFFu) | 0xFFFF0000u;   // lim(5..6), then never
+  uint32_t i = 0, prev = 0, kl = 0, kd = 0;
+  bool eob = false;
+#pragma unroll 1
+  while (i < n) {
+    v = br.peek();
+    const uint32_t x  = simt::brev(v) >> 25;                         // 7 code bits, first bit on top
+    const uint32_t xx = x * 0x01010101u;
+    const uint32_t l  = 1u + (uint32_t)((simt::popc(__vcmpgeu4(xx, limA)) + simt::popc(__vcmpgeu4(xx, limB))) >> 3);
+    const uint32_t base = (uint32_t)(lims >> (8u * (l - 1u))) & 255u;
+    const uint32_t idx  = ((uint32_t)(offs >> (8u * l)) & 255u) + ((x - base) >> (7u - l));
+    const uint32_t sym  = (uint32_t)(idx < 12u ? slo >> (5u * idx) : shi >> (5u * (idx - 12u))) & 31u;
+    v >>= l;
+    uint32_t rep = 1, val = sym, xb = 0;
+    if (sym >= 16u) {
+      if (sym == 16u)      { if (i == 0u) return false; xb = 2; rep = 3u + (v & 3u); val = prev; }
+      else if (sym == 17u) { xb = 3; rep = 3u + (v & 7u); val = 0; }
+      else                 { xb = 7; rep = 11u + (v & 127u); val = 0; }
+      if (i + rep > n) return false;
+      if (sym != 16u) prev = 0;
+    } else {
+      prev = sym;
+    }
+    if (val) {
+      const uint32_t c  = 32768u >> val;
+      const uint32_t nl = i >= hlit ? 0u : (hlit - i < rep ? hlit - i : rep);
+      kl += nl * c;
+      kd += (rep - nl) * c;
+      if (i <= 256u && 256u < i + rep) eob = true;
+    }
+    i += rep;
+    br.skip(l + xb);
+    used += l + xb;
+    if (kl > 32768u) return false;
+  }
+  return kl == 32768u && eob && kd != 0u && kd <= 32768u && pc + used <= end_bit;
+}
+
+struct FindSmem {
+  uint16_t list[128];     // positions of the current 128 that pass stage 1
+  uint32_t pend[64];      // granule-relative positions that passed stage 2, in increasing order
+};
+
 template <int WARPS>
 __global__ void __launch_bounds__(WARPS * 32)
 find_block_starts_kernel(const uint8_t* __restrict__ src, uint32_t srclen, uint32_t body, uint32_t ngran,
-                         uint64_t* __restrict__ found) {
-  extern __shared__ __align__(16) unsigned char smem_raw[];
+                         uint32_t granule_bytes, uint64_t* __restrict__ found) {
+  __shared__ FindSmem fsm[WARPS];
+  __shared__ uint8_t  kraft9[512];
+  for (uint32_t i = threadIdx.x; i < 512u; i += WARPS * 32) {
+    const uint32_t a = i & 7u, b = (i >> 3) & 7u, c = i >> 6;
+    kraft9[i] = (uint8_t)((a ? 128u >> a : 0u) + (b ? 128u >> b : 0u) + (c ? 128u >> c : 0u));
+  }
+  __syncthreads();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  WarpSmem& sm = reinterpret_cast<WarpSmem*>(smem_raw)[warp];
+  FindSmem& fs = fsm[warp];
   const uint32_t g = blockIdx.x * WARPS + warp;
   if (g >= ngran) return;
-  Lane<32> L;
-  L.gmask = kFull; L.lane = lane; L.wlane = lane;
+  const unsigned lt = simt::lanemask_lt();
   const uint32_t mis      = (uint32_t)((uintptr_t)src & 3u);
   const uint64_t base_bit = (uint64_t)mis * 8u;
   const uint64_t end_bit  = base_bit + (uint64_t)srclen * 8u;
   const uint32_t* words   = reinterpret_cast<const uint32_t*>((uintptr_t)src - mis);
   const uint32_t  wend    = (uint32_t)(((uint64_t)mis + srclen + 3u) >> 2);
-  const uint64_t p0 = base_bit + ((uint64_t)body + (uint64_t)g * kGranuleBytes) * 8u;
-  uint64_t       p1 = p0 + (uint64_t)kGranuleBytes * 8u;
+  const uint64_t p0 = base_bit + ((uint64_t)body + (uint64_t)g * granule_bytes) * 8u;
+  uint64_t       p1 = p0 + (uint64_t)granule_bytes * 8u;
   if (p1 + 96u > end_bit) p1 = end_bit > 96u ? end_bit - 96u : 0u;     // a header needs room
   uint64_t result = kNoCandidate;
-#pragma unroll 1
-  for (uint64_t pb = p0; pb < p1 && result == kNoCandidate; pb += 32u) {
-    const uint64_t p  = pb + (uint64_t)lane;
-    const uint32_t wi = (uint32_t)(p >> 5), sh = (uint32_t)(p & 31u);
-    const uint32_t w0 = wi < wend ? simt::ld_in32(words + wi) : 0u;
-    const uint32_t w1 = wi + 1 < wend ? simt::ld_in32(words + wi + 1) : 0u;
-    const uint32_t w2 = wi + 2 < wend ? simt::ld_in32(words + wi + 2) : 0u;
-    const uint32_t w3 = wi + 3 < wend ? simt::ld_in32(words + wi + 3) : 0u;
-    const bool ok = p < p1 && header_plausible(simt::funnel_r(w0, w1, sh), simt::funnel_r(w1, w2, sh),
-                                               simt::funnel_r(w2, w3, sh));
-    unsigned m = simt::ballot(kFull, ok);
-#pragma unroll 1
-    while (m) {
-      const int l = simt::ffs(m) - 1;
-      m &= m - 1u;
-      const uint64_t pc = pb + (uint64_t)l;
-      BitReader br;
-      br.w = words; br.wend = wend;
-      br.seek(pc + 3u);
-      bool fixed_ready = false;
-      simt::syncwarp(kFull);
-      const uint32_t reason = huffman_block_setup<32>(L, sm.lit, sm.dist, sm.s, br, end_bit, 2u, fixed_ready);
-      simt::syncwarp(kFull);
-      if (reason) continue;
-      BitReader hr;
-      hr.w = words; hr.wend = wend;
-      hr.seek(pc);
-      const uint32_t hv = hr.peek();
-      const uint32_t hlit = ((hv >> 3) & 31u) + 257u, hdist = ((hv >> 8) & 31u) + 1u;
-      uint32_t kl = 0, kd = 0;
-      for (uint32_t i = (uint32_t)lane; i < hlit; i += 32u) { const uint32_t len = sm.s.lens[i]; kl += len ? (32768u >> len) : 0u; }
-      for (uint32_t i = (uint32_t)lane; i < hdist; i += 32u) { const uint32_t len = sm.s.lens[hlit + i]; kd += len ? (32768u >> len) : 0u; }
-      kl = simt::reduce_add(kFull, kl);
-      kd = simt::reduce_add(kFull, kd);
-      const bool good = kl == 32768u && sm.s.lens[256] != 0u && kd != 0u;
-      simt::syncwarp(kFull);
-      if (good) { result = pc - base_bit; break; }
+  uint32_t npend = 0;
+
+  // stage 3 over the first (up to) 32 pending candidates
+  auto parse_round = [&]() {
+    const uint32_t take = npend < 32u ? npend : 32u;
+    bool pass = false;
+    uint64_t pc = 0;
+    if ((uint32_t)lane < take) {
+      pc = p0 + fs.pend[lane];
+      pass = header_full_check(words, wend, pc, end_bit);
     }
+    const unsigned m = simt::ballot(kFull, pass);
+    if (m) {
+      const int l = simt::ffs(m) - 1;
+      result = p0 + fs.pend[l] - base_bit;
+    } else {
+      const uint32_t keep = npend - take;
+      const uint32_t v = (uint32_t)lane < keep ? fs.pend[32 + lane] : 0u;
+      simt::syncwarp(kFull);
+      if ((uint32_t)lane < keep) fs.pend[lane] = v;
+      npend = keep;
+    }
+    simt::syncwarp(kFull);
+  };
+
+#pragma unroll 1
+  for (uint64_t pb = p0; pb < p1 && result == kNoCandidate; pb += 128u) {
+    uint32_t cnt = 0;
+#pragma unroll
+    for (uint32_t u = 0; u < 4u; u++) {
+      const uint64_t p  = pb + 32u * u + (uint32_t)lane;
+      const uint32_t wi = (uint32_t)(p >> 5), sh = (uint32_t)(p & 31u);
+      const uint32_t w0 = wi < wend ? simt::ld_in32(words + wi) : 0u;
+      const uint32_t w1 = wi + 1 < wend ? simt::ld_in32(words + wi + 1) : 0u;
+      const bool ok = p < p1 && header_cheap(simt::funnel_r(w0, w1, sh));
+      const unsigned m = simt::ballot(kFull, ok);
+      if (ok) fs.list[cnt + (uint32_t)simt::popc(m & lt)] = (uint16_t)(32u * u + (uint32_t)lane);
+      cnt += (uint32_t)simt::popc(m);
+    }
+    simt::syncwarp(kFull);
+#pragma unroll 1
+    for (uint32_t k0 = 0; k0 < cnt && result == kNoCandidate; k0 += 32u) {
+      const bool has = k0 + (uint32_t)lane < cnt;
+      bool good = false;
+      uint64_t p = 0;
+      if (has) {
+        p = pb + fs.list[k0 + (uint32_t)lane];
+        const uint32_t wi = (uint32_t)(p >> 5), sh = (uint32_t)(p & 31u);
+        const uint32_t w0 = wi < wend ? simt::ld_in32(words + wi) : 0u;
+        const uint32_t w1 = wi + 1 < wend ? simt::ld_in32(words + wi + 1) : 0u;
+        const uint32_t w2 = wi + 2 < wend ? simt::ld_in32(words + wi + 2) : 0u;
+        const uint32_t w3 = wi + 3 < wend ? simt::ld_in32(words + wi + 3) : 0u;
+        good = precode_complete(simt::funnel_r(w0, w1, sh), simt::funnel_r(w1, w2, sh), simt::funnel_r(w2, w3, sh), kraft9);
+      }
+      const unsigned m = simt::ballot(kFull, good);
+      if (good) fs.pend[npend + (uint32_t)simt::popc(m & lt)] = (uint32_t)(p - p0);
+      npend += (uint32_t)simt::popc(m);
+      simt::syncwarp(kFull);
+      if (npend >= 32u) parse_round();
+    }
+    simt::syncwarp(kFull);
   }
+#pragma unroll 1
+  while (result == kNoCandidate && npend > 0u) parse_round();
   if (lane == 0) found[g] = result;
 }
 
@@ -255,45 +419,122 @@ DEFL_DEV uint32_t resolve_marker(const uint16_t* sym, const uint64_t* off, uint3
 }
 
 #ifdef __CUDACC__
+// D runs as two kernels so that no marker needs more than one look-up in fast memory:
+//   D1 window_resolve_kernel : for every chunk c >= 1 the 32 KiB of output before it, as resolved bytes
+//                              (wbuf[c-1]); only these tail symbols follow marker chains through HBM.
+//   D2 marker_resolve_kernel : a block owns 64 KiB of output; per chunk it touches it stages wbuf[c-1] in
+//                              shared memory, streams the symbols (16-byte loads), replaces markers from the
+//                              staged window, stores 8 bytes at a time and keeps Adler-32 partial sums.
+constexpr uint32_t kWinBytes        = 32768;
+constexpr uint32_t kResolvePerBlock = 65536;      // output bytes per D2 block
+
 __global__ void __launch_bounds__(256)
-marker_resolve_kernel(const uint16_t* __restrict__ sym, const uint64_t* __restrict__ off, uint32_t nchunk,
-                      uint8_t* __restrict__ dst, uint64_t total, uint32_t* __restrict__ partial) {
-  __shared__ uint32_t sa[8], sw[8];
-  const uint64_t per_block = 256u * 16u;
-  const uint64_t b0 = (uint64_t)blockIdx.x * per_block;
-  uint32_t A = 0;
-  uint64_t W = 0;
-  // the chunk that holds this block's first position (blocks are small next to chunks: walk forward from it)
-  uint32_t c = 0;
-  {
-    uint32_t lo = 0, hi = nchunk;
-    while (hi - lo > 1u) { const uint32_t mid = (lo + hi) >> 1; if (off[mid] <= b0) lo = mid; else hi = mid; }
-    c = lo;
-  }
+window_resolve_kernel(const uint16_t* __restrict__ sym, const uint64_t* __restrict__ off, uint32_t nchunk,
+                      uint8_t* __restrict__ wbuf) {
+  const uint32_t c  = 1u + blockIdx.x / 16u;                      // 16 blocks x 2048 symbols per window
+  const uint32_t k0 = (blockIdx.x % 16u) * 2048u + threadIdx.x * 8u;
+  if (c >= nchunk) return;
+  const uint64_t base = off[c] - kWinBytes;                       // the host made sure off[c] >= 32 KiB
+  uint32_t s[8];
+#pragma unroll
+  for (int k = 0; k < 8; k++) s[k] = sym[base + k0 + (uint32_t)k];
+  if ((s[0] | s[1] | s[2] | s[3] | s[4] | s[5] | s[6] | s[7]) & 0x8000u) {
 #pragma unroll 1
-  for (int it = 0; it < 16; it++) {
-    const uint64_t i = b0 + (uint64_t)it * 256u + threadIdx.x;
-    if (i < total) {
-      uint32_t cc = c;
-      while (cc + 1u < nchunk && off[cc + 1u] <= i) cc++;
-      const uint32_t s = resolve_marker(sym, off, cc, i);
-      dst[i] = (uint8_t)s;
-      A += s;
-      W += (uint64_t)(i % kAdlerMod) * s;
+    for (int k = 0; k < 8; k++) {
+      if (!(s[k] & 0x8000u)) continue;
+      const uint64_t i = base + k0 + (uint32_t)k;
+      uint32_t cc = c - 1u;
+      while (off[cc] > i) cc--;
+      s[k] = resolve_marker(sym, off, cc, i);
     }
   }
-  uint32_t w32 = (uint32_t)(W % kAdlerMod);
+  const uint32_t lo = s[0] | (s[1] << 8) | (s[2] << 16) | (s[3] << 24);
+  const uint32_t hi = s[4] | (s[5] << 8) | (s[6] << 16) | (s[7] << 24);
+  *reinterpret_cast<uint2*>(wbuf + (size_t)(c - 1u) * kWinBytes + k0) = make_uint2(lo, hi);
+}
+
+__global__ void __launch_bounds__(256)
+marker_resolve_kernel(const uint16_t* __restrict__ sym, const uint64_t* __restrict__ off, uint32_t nchunk,
+                      const uint8_t* __restrict__ wbuf, uint8_t* __restrict__ dst, uint64_t total,
+                      uint32_t* __restrict__ partial) {
+  __shared__ __align__(16) uint8_t win[kWinBytes];
+  __shared__ uint32_t sa[8], sw[8], sc0;
+  const uint64_t b0 = (uint64_t)blockIdx.x * kResolvePerBlock;
+  const uint64_t b1 = b0 + kResolvePerBlock < total ? b0 + kResolvePerBlock : total;
+  if (threadIdx.x == 0) {          // the chunk that holds this block's first position
+    uint32_t lo = 0, hi = nchunk;
+    while (hi - lo > 1u) { const uint32_t mid = (lo + hi) >> 1; if (off[mid] <= b0) lo = mid; else hi = mid; }
+    sc0 = lo;
+  }
+  __syncthreads();
+  uint32_t   c = sc0;
+  uint32_t   A = 0;
+  uint64_t   W = 0;
+  const bool dst_aligned = ((uintptr_t)dst & 7u) == 0u;
+  uint64_t   pos = b0;
+#pragma unroll 1
+  while (pos < b1) {               // one round per chunk the block touches (block-uniform)
+    while (c + 1u < nchunk && off[c + 1u] <= pos) c++;
+    const uint64_t cend = c + 1u < nchunk ? off[c + 1u] : total;
+    const uint64_t send = cend < b1 ? cend : b1;
+    __syncthreads();
+    if (c >= 1u) {
+      const uint4* wsrc = reinterpret_cast<const uint4*>(wbuf + (size_t)(c - 1u) * kWinBytes);
+      for (uint32_t i = threadIdx.x; i < kWinBytes / 16u; i += 256u) reinterpret_cast<uint4*>(win)[i] = __ldg(wsrc + i);
+    }
+    __syncthreads();
+#pragma unroll 1
+    for (uint64_t i0 = (pos & ~7ull) + threadIdx.x * 8u; i0 < send; i0 += 2048u) {
+      const uint32_t j0 = (uint32_t)(i0 - (b0 & ~7ull));     // relative to the block's aligned start
+      uint32_t s[8];
+      if (i0 >= pos && i0 + 8u <= send) {
+        const uint4 v = __ldcs(reinterpret_cast<const uint4*>(sym + i0));
+        s[0] = v.x & 0xFFFFu; s[1] = v.x >> 16; s[2] = v.y & 0xFFFFu; s[3] = v.y >> 16;
+        s[4] = v.z & 0xFFFFu; s[5] = v.z >> 16; s[6] = v.w & 0xFFFFu; s[7] = v.w >> 16;
+        if ((v.x | v.y | v.z | v.w) & 0x80008000u) {
+#pragma unroll
+          for (int k = 0; k < 8; k++) if (s[k] & 0x8000u) s[k] = win[s[k] & 0x7FFFu];
+        }
+        const uint32_t lo = s[0] | (s[1] << 8) | (s[2] << 16) | (s[3] << 24);
+        const uint32_t hi = s[4] | (s[5] << 8) | (s[6] << 16) | (s[7] << 24);
+        if (dst_aligned) {
+          __stcs(reinterpret_cast<uint2*>(dst + i0), make_uint2(lo, hi));
+        } else {
+#pragma unroll
+          for (int k = 0; k < 8; k++) dst[i0 + k] = (uint8_t)s[k];
+        }
+        const uint32_t sum = __dp4a(lo, 0x01010101u, __dp4a(hi, 0x01010101u, 0u));
+        const uint32_t q   = __dp4a(lo, 0x03020100u, __dp4a(hi, 0x07060504u, 0u));
+        A += sum;
+        W += (uint64_t)j0 * sum + q;
+      } else {                     // a group cut by the chunk's or the block's ends
+#pragma unroll 1
+        for (uint32_t k = 0; k < 8u; k++) {
+          const uint64_t i = i0 + k;
+          if (i < pos || i >= send) continue;
+          uint32_t x = sym[i];
+          if (x & 0x8000u) x = win[x & 0x7FFFu];
+          dst[i] = (uint8_t)x;
+          A += x;
+          W += (uint64_t)(j0 + k) * x;
+        }
+      }
+    }
+    pos = send;
+  }
   for (int o = 16; o > 0; o >>= 1) {
     A += __shfl_xor_sync(0xFFFFFFFFu, A, o);
-    w32 += __shfl_xor_sync(0xFFFFFFFFu, w32, o);
+    W += __shfl_xor_sync(0xFFFFFFFFu, W, o);
   }
-  if ((threadIdx.x & 31) == 0) { sa[threadIdx.x >> 5] = A; sw[threadIdx.x >> 5] = w32 % kAdlerMod; }
+  if ((threadIdx.x & 31) == 0) { sa[threadIdx.x >> 5] = A; sw[threadIdx.x >> 5] = (uint32_t)(W % kAdlerMod); }
   __syncthreads();
   if (threadIdx.x == 0) {
     uint32_t ta = 0, tw = 0;
-    for (int k = 0; k < 8; k++) { ta += sa[k]; tw = (tw + sw[k]) % kAdlerMod; }
-    partial[2 * blockIdx.x]     = ta % kAdlerMod;
-    partial[2 * blockIdx.x + 1] = tw;
+    for (int k = 0; k < 8; k++) { ta += sa[k]; tw += sw[k]; }
+    ta %= kAdlerMod;
+    // sum of i * x over the block = (origin mod M) * sum x + sum j * x, j counted from the aligned origin
+    partial[2 * blockIdx.x]     = ta;
+    partial[2 * blockIdx.x + 1] = (uint32_t)((((b0 & ~7ull) % kAdlerMod) * ta + tw) % kAdlerMod);
   }
 }
 

@@ -381,6 +381,13 @@ DEFL_DEV WarpScratch scratch_of(void* base) {
   return s;
 }
 
+// Where the COUNT pass of the split decode keeps a chunk's tokens for the DECODE pass (split_decode.cuh).
+struct TokSink {
+  uint32_t* buf;      // nullptr: nothing is kept
+  uint32_t  cap, n;   // budget and fill, in tokens
+  bool      ok;       // false once the budget ran out (n is meaningless then)
+};
+
 // Decode from absolute bit `cur` (a token boundary inside a Huffman block whose tables are in sm) as far
 // as one window reaches.  On return `cur` is where the stream goes on; the result is LS_OK (window done,
 // block goes on), LS_EOB (block ended at cur), or LS_FAIL | reason << 8.
@@ -388,7 +395,7 @@ DEFL_DEV WarpScratch scratch_of(void* base) {
 template <typename SYM, bool COUNT>
 DEFL_DEV uint32_t decode_window(WarpSmem& sm, const WarpScratch& sc, int lane, const uint32_t* words,
                                 uint32_t wend, uint64_t end_bit, uint64_t& cur, SYM* dst, uint32_t cap,
-                                uint32_t& pos, uint32_t hist) {
+                                uint32_t& pos, uint32_t hist, TokSink* sink = nullptr) {
   const uint32_t bw   = (uint32_t)(cur >> 5);
   const uint32_t rel0 = (uint32_t)(cur & 31u);
   const uint64_t left64 = end_bit - ((uint64_t)bw << 5);
@@ -430,9 +437,32 @@ DEFL_DEV uint32_t decode_window(WarpSmem& sm, const WarpScratch& sc, int lane, c
 
   uint32_t reason = R_NONE;
   if (COUNT) {
-    // every lane adds up its own true tokens
     uint32_t bytes = 0;
-    if (lane <= last) {
+    if (sink && sink->buf && sink->ok) {
+      // the warp walks the true tokens in stream order: adds up their bytes and keeps them (coalesced)
+      uint32_t w = sink->n;
+      bool     ok = true;
+#pragma unroll 1
+      for (int L = 0; L <= last; L++) {
+        const uint32_t nf = simt::shfl(kFull, tj.nf, L);
+        const uint32_t m  = simt::shfl(kFull, tj.m, L);
+        const uint32_t n  = simt::shfl(kFull, tj.n, L);
+#pragma unroll 1
+        for (int part = 0; part < 2; part++) {
+          const uint32_t* p = part == 0 ? sc.fix + (uint32_t)L * kFixCap : sc.spec + (uint32_t)L * kSpecCap + m;
+          const uint32_t  c = part == 0 ? nf : (n > m ? n - m : 0u);
+          if (c > sink->cap - w) ok = false;
+          for (uint32_t i = (uint32_t)lane; i < c; i += 32u) {
+            const uint32_t t = simt::ld_tok(p + i);
+            bytes += (t >> 31) ? (t & 511u) : ((t >> 24) & 7u);
+            if (ok) sink->buf[w + i] = t;
+          }
+          if (ok) w += c;
+        }
+      }
+      sink->n = w;
+      sink->ok = ok;
+    } else if (lane <= last) {   // every lane adds up its own true tokens
       for (uint32_t i = 0; i < tj.nf; i++) {
         const uint32_t t = simt::ld_tok(fix + i);
         bytes += (t >> 31) ? (t & 511u) : ((t >> 24) & 7u);

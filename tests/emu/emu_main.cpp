@@ -203,6 +203,8 @@ struct ChunkJob {
   uint32_t            cap;
   bool                count;
   defl::SplitChunkOut* out;
+  uint32_t*           tok;      // count: where tokens are kept; decode: tokens to replay (with ntok)
+  uint32_t            tokcap, ntok;
 };
 
 void* chunk_main(void* arg) {
@@ -211,24 +213,28 @@ void* chunk_main(void* arg) {
   simt::t_lane  = j->lane;
   defl::SplitChunkOut o;
   const uint32_t hist = j->me == 0 ? 0u : 32768u;
-  if (j->count)
+  if (j->count) {
+    defl::TokSink sink;
+    sink.buf = j->tok; sink.cap = j->tokcap; sink.n = 0; sink.ok = j->tok != nullptr;
     defl::inflate_chunk_warp<uint16_t, true>(*j->sm, defl::scratch_of(j->scratch), j->lane, j->src, j->srclen, j->cand,
-                                             j->ncand, j->me, nullptr, 0xFFFFFFFFu, hist, o);
-  else
+                                             j->ncand, j->me, nullptr, 0xFFFFFFFFu, hist, o, &sink);
+  } else {
     defl::inflate_chunk_warp<uint16_t, false>(*j->sm, defl::scratch_of(j->scratch), j->lane, j->src, j->srclen, j->cand,
-                                              j->ncand, j->me, j->dst, j->cap, hist, o);
+                                              j->ncand, j->me, j->dst, j->cap, hist, o, nullptr, j->tok, j->ntok);
+  }
   if (j->lane == 0) *j->out = o;
   return nullptr;
 }
 
 void run_chunk(defl::WarpSmem* sm, void* scratch, const uint8_t* src, uint32_t srclen, const uint64_t* cand,
-               uint32_t ncand, uint32_t me, uint16_t* dst, uint32_t cap, bool count, defl::SplitChunkOut* out) {
+               uint32_t ncand, uint32_t me, uint16_t* dst, uint32_t cap, bool count, defl::SplitChunkOut* out,
+               uint32_t* tok = nullptr, uint32_t tokcap = 0, uint32_t ntok = defl::kNoTokens) {
   simt::Group grp;
   grp.G = 32;
   pthread_barrier_init(&grp.bar, nullptr, 32);
   std::vector<ChunkJob>  jobs(32);
   std::vector<pthread_t> th(32);
-  for (int i = 0; i < 32; i++) jobs[i] = ChunkJob{&grp, i, sm, scratch, src, srclen, cand, ncand, me, dst, cap, count, out};
+  for (int i = 0; i < 32; i++) jobs[i] = ChunkJob{&grp, i, sm, scratch, src, srclen, cand, ncand, me, dst, cap, count, out, tok, tokcap, ntok};
   for (int i = 1; i < 32; i++) pthread_create(&th[i], nullptr, chunk_main, &jobs[i]);
   chunk_main(&jobs[0]);
   for (int i = 1; i < 32; i++) pthread_join(th[i], nullptr);
@@ -237,13 +243,23 @@ void run_chunk(defl::WarpSmem* sm, void* scratch, const uint8_t* src, uint32_t s
 
 }  // namespace
 
+static long g_replayed = 0;
+extern "C" long emu_split_replayed() { return g_replayed; }
+
 // cand[0] must be the first block of the stream.  Returns produced bytes, or -1 - (failing step).
 extern "C" long emu_split_inflate(const uint8_t* src, uint32_t srclen, const uint64_t* cand, uint32_t ncand,
                                   uint8_t* dst, uint32_t cap, uint64_t* end_bit) {
   defl::WarpSmem* sm = static_cast<defl::WarpSmem*>(aligned_alloc(64, (sizeof(defl::WarpSmem) + 63) & ~63ul));
   void* scratch = aligned_alloc(64, defl::kWarpScratchBytes);
   std::vector<defl::SplitChunkOut> outs(ncand);
-  for (uint32_t i = 0; i < ncand; i++) run_chunk(sm, scratch, src, srclen, cand, ncand, i, nullptr, 0, true, &outs[i]);
+  // every chunk keeps its tokens in the count pass (2 per compressed byte of budget, as the host does);
+  // odd chunks replay them in the decode pass, even chunks decode again: both ways are exercised
+  std::vector<std::vector<uint32_t>> toks(ncand);
+  for (uint32_t i = 0; i < ncand; i++) {
+    const uint64_t b0 = cand[i] >> 3, b1 = i + 1 < ncand ? cand[i + 1] >> 3 : srclen;
+    toks[i].resize(2 * (b1 - b0) + 1);
+    run_chunk(sm, scratch, src, srclen, cand, ncand, i, nullptr, 0, true, &outs[i], toks[i].data(), (uint32_t)toks[i].size() - 1);
+  }
   std::vector<uint32_t> chain;
   std::vector<uint64_t> off;
   uint64_t total = 0;
@@ -261,8 +277,12 @@ extern "C" long emu_split_inflate(const uint8_t* src, uint32_t srclen, const uin
     std::vector<uint16_t> sym(total + 8, 0xFFFF);
     for (size_t k = 0; k < chain.size() && rc == 0; k++) {
       defl::SplitChunkOut o2;
-      run_chunk(sm, scratch, src, srclen, cand, ncand, chain[k], sym.data() + off[k], outs[chain[k]].out_bytes, false, &o2);
-      if (o2.status != outs[chain[k]].status || o2.out_bytes != outs[chain[k]].out_bytes) rc = -4;
+      const bool replay = (k & 1) && outs[chain[k]].ntok != defl::kNoTokens;
+      run_chunk(sm, scratch, src, srclen, cand, ncand, chain[k], sym.data() + off[k], outs[chain[k]].out_bytes, false, &o2,
+                toks[chain[k]].data(), 0, replay ? outs[chain[k]].ntok : defl::kNoTokens);
+      if (replay ? (o2.status != defl::CH_REPLAYED || o2.out_bytes != outs[chain[k]].out_bytes)
+                 : (o2.status != outs[chain[k]].status || o2.out_bytes != outs[chain[k]].out_bytes)) rc = -4;
+      if (replay) g_replayed++;
     }
     if (rc == 0) {
       uint32_t cc = 0;

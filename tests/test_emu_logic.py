@@ -187,3 +187,5 @@ def test_split_chunks_and_markers_logic(emu):
         assert n == len(raw), (kind, n)
         assert dst.raw[:n] == raw, kind
         assert (end_bit.value + 7) // 8 == len(z) - 4
+    emu.emu_split_replayed.restype = ctypes.c_long
+    assert emu.emu_split_replayed() > 0      # some chunks took the kept-token replay path
