@@ -303,9 +303,11 @@ DEFL_DEV bool header_full_check(const uint32_t* words, uint32_t wend, uint64_t p
   return kl == 32768u && eob && kd != 0u && kd <= 32768u && pc + used <= end_bit;
 }
 
+constexpr uint32_t kFindSpan = 1024;   // bit positions per scan step: one 32-bit word per lane
+
 struct FindSmem {
-  uint16_t list[128];     // positions of the current 128 that pass stage 1
-  uint32_t pend[64];      // granule-relative positions that passed stage 2, in increasing order
+  uint16_t list[kFindSpan];   // positions of the current span that pass stage 1, in increasing order
+  uint32_t pend[64];          // granule-relative positions that passed stage 2, in increasing order
 };
 
 template <int WARPS>
@@ -339,11 +341,7 @@ find_block_starts_kernel(const uint8_t* __restrict__ src, uint32_t srclen, uint3
   auto parse_round = [&]() {
     const uint32_t take = npend < 32u ? npend : 32u;
     bool pass = false;
-    uint64_t pc = 0;
-    if ((uint32_t)lane < take) {
-      pc = p0 + fs.pend[lane];
-      pass = header_full_check(words, wend, pc, end_bit);
-    }
+    if ((uint32_t)lane < take) pass = header_full_check(words, wend, p0 + fs.pend[lane], end_bit);
     const unsigned m = simt::ballot(kFull, pass);
     if (m) {
       const int l = simt::ffs(m) - 1;
@@ -359,18 +357,33 @@ find_block_starts_kernel(const uint8_t* __restrict__ src, uint32_t srclen, uint3
   };
 
 #pragma unroll 1
-  for (uint64_t pb = p0; pb < p1 && result == kNoCandidate; pb += 128u) {
-    uint32_t cnt = 0;
+  for (uint64_t pb = p0 & ~31ull; pb < p1 && result == kNoCandidate; pb += kFindSpan) {
+    // stage 1, 32 positions per lane with plain bit logic: bit k of sK = input bit (position + K)
+    const uint64_t q  = pb + 32u * (uint32_t)lane;             // this lane's first position (word aligned)
+    const uint32_t wi = (uint32_t)(q >> 5);
+    const uint32_t w0 = wi < wend ? simt::ld_in32(words + wi) : 0u;
+    const uint32_t w1 = wi + 1 < wend ? simt::ld_in32(words + wi + 1) : 0u;
+#define DEFL_S(K) simt::funnel_r(w0, w1, K)
+    uint32_t m = ~DEFL_S(1) & DEFL_S(2)                                   // BTYPE = 2
+                 & ~(DEFL_S(4) & DEFL_S(5) & DEFL_S(6) & DEFL_S(7))        // HLIT  < 30
+                 & ~(DEFL_S(9) & DEFL_S(10) & DEFL_S(11) & DEFL_S(12));    // HDIST < 30
+#undef DEFL_S
+    if (q < p0) m = p0 - q >= 32u ? 0u : m & (0xFFFFFFFFu << (uint32_t)(p0 - q));
+    if (q + 32u > p1) m = q >= p1 ? 0u : m & ((1u << (uint32_t)(p1 - q)) - 1u);
+    // compact: every lane appends its positions at its prefix offset
+    const uint32_t c = (uint32_t)simt::popc(m);
+    uint32_t inc = c;
 #pragma unroll
-    for (uint32_t u = 0; u < 4u; u++) {
-      const uint64_t p  = pb + 32u * u + (uint32_t)lane;
-      const uint32_t wi = (uint32_t)(p >> 5), sh = (uint32_t)(p & 31u);
-      const uint32_t w0 = wi < wend ? simt::ld_in32(words + wi) : 0u;
-      const uint32_t w1 = wi + 1 < wend ? simt::ld_in32(words + wi + 1) : 0u;
-      const bool ok = p < p1 && header_cheap(simt::funnel_r(w0, w1, sh));
-      const unsigned m = simt::ballot(kFull, ok);
-      if (ok) fs.list[cnt + (uint32_t)simt::popc(m & lt)] = (uint16_t)(32u * u + (uint32_t)lane);
-      cnt += (uint32_t)simt::popc(m);
+    for (int d = 1; d < 32; d <<= 1) {
+      const uint32_t t = simt::shfl_up(kFull, inc, d);
+      if (lane >= d) inc += t;
+    }
+    const uint32_t cnt = simt::shfl(kFull, inc, 31);
+    uint32_t o = inc - c;
+    while (m) {
+      const uint32_t b = (uint32_t)simt::ffs(m) - 1u;
+      m &= m - 1u;
+      fs.list[o++] = (uint16_t)(32u * (uint32_t)lane + b);
     }
     simt::syncwarp(kFull);
 #pragma unroll 1
@@ -380,16 +393,16 @@ find_block_starts_kernel(const uint8_t* __restrict__ src, uint32_t srclen, uint3
       uint64_t p = 0;
       if (has) {
         p = pb + fs.list[k0 + (uint32_t)lane];
-        const uint32_t wi = (uint32_t)(p >> 5), sh = (uint32_t)(p & 31u);
-        const uint32_t w0 = wi < wend ? simt::ld_in32(words + wi) : 0u;
-        const uint32_t w1 = wi + 1 < wend ? simt::ld_in32(words + wi + 1) : 0u;
-        const uint32_t w2 = wi + 2 < wend ? simt::ld_in32(words + wi + 2) : 0u;
-        const uint32_t w3 = wi + 3 < wend ? simt::ld_in32(words + wi + 3) : 0u;
-        good = precode_complete(simt::funnel_r(w0, w1, sh), simt::funnel_r(w1, w2, sh), simt::funnel_r(w2, w3, sh), kraft9);
+        const uint32_t xi = (uint32_t)(p >> 5), sh = (uint32_t)(p & 31u);
+        const uint32_t x0 = xi < wend ? simt::ld_in32(words + xi) : 0u;
+        const uint32_t x1 = xi + 1 < wend ? simt::ld_in32(words + xi + 1) : 0u;
+        const uint32_t x2 = xi + 2 < wend ? simt::ld_in32(words + xi + 2) : 0u;
+        const uint32_t x3 = xi + 3 < wend ? simt::ld_in32(words + xi + 3) : 0u;
+        good = precode_complete(simt::funnel_r(x0, x1, sh), simt::funnel_r(x1, x2, sh), simt::funnel_r(x2, x3, sh), kraft9);
       }
-      const unsigned m = simt::ballot(kFull, good);
-      if (good) fs.pend[npend + (uint32_t)simt::popc(m & lt)] = (uint32_t)(p - p0);
-      npend += (uint32_t)simt::popc(m);
+      const unsigned gm = simt::ballot(kFull, good);
+      if (good) fs.pend[npend + (uint32_t)simt::popc(gm & lt)] = (uint32_t)(p - p0);
+      npend += (uint32_t)simt::popc(gm);
       simt::syncwarp(kFull);
       if (npend >= 32u) parse_round();
     }
