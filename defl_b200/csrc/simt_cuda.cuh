@@ -60,11 +60,14 @@ DEFL_DEV long long ticks() { return clock64(); }
 DEFL_DEV uint32_t ld_out8(const uint8_t* p) { return __ldcg(p); }
 DEFL_DEV uint32_t ld_out(const uint8_t* p) { return __ldcg(p); }
 DEFL_DEV uint32_t ld_out(const uint16_t* p) { return __ldcg(p); }
+DEFL_DEV uint32_t ld_outw(const uint32_t* p) { return __ldcg(p); }      // the aligned word around a match source
 
 // ---- used by the warp-per-stream decoder (warp_decode.cuh) ------------------------------------------
 DEFL_DEV bool     any(unsigned mask, bool p) { return __any_sync(mask, p); }
 DEFL_DEV int      clz(uint32_t v) { return __clz((int)v); }
 DEFL_DEV uint32_t reduce_add(unsigned mask, uint32_t v) { return __reduce_add_sync(mask, v); }
+DEFL_DEV uint32_t reduce_min(unsigned mask, uint32_t v) { return __reduce_min_sync(mask, v); }
+DEFL_DEV uint32_t reduce_max(unsigned mask, uint32_t v) { return __reduce_max_sync(mask, v); }
 // tokens written to the global scratch by one lane and read back by the whole warp: L2 only
 DEFL_DEV uint32_t ld_tok(const uint32_t* p) { return __ldcg(p); }
 

@@ -52,23 +52,24 @@ struct WarpSmem {
 };
 static_assert(sizeof(WarpSmem) % 16 == 0, "WarpSmem alignment");
 
-// ---- per-lane bit reader: a 96-bit window in registers, positions relative to the window base word ----
+// ---- per-lane bit reader: a 96-bit window in registers plus one word already on its way (w3 is only
+// ever moved, so its load has a whole refill period to land); positions relative to the window base word ----
 struct SubReader {
   const uint32_t* w;
   uint32_t        wend, widx;
-  uint32_t        w0, w1, w2;
+  uint32_t        w0, w1, w2, w3;
   uint32_t        bo;
 
   DEFL_DEV uint32_t ld(uint32_t i) const { return i < wend ? simt::ld_in32(w + i) : 0u; }
   DEFL_DEV void seek(uint32_t word, uint32_t bit) {
     widx = word + (bit >> 5);
     bo   = bit & 31u;
-    w0 = ld(widx); w1 = ld(widx + 1); w2 = ld(widx + 2);
+    w0 = ld(widx); w1 = ld(widx + 1); w2 = ld(widx + 2); w3 = ld(widx + 3);
   }
   DEFL_DEV void consume(uint32_t n) {     // n <= 48, bo < 32 on entry
     bo += n;
-    if (bo >= 32u) { w0 = w1; w1 = w2; widx++; bo -= 32u; w2 = ld(widx + 2); }
-    if (bo >= 32u) { w0 = w1; w1 = w2; widx++; bo -= 32u; w2 = ld(widx + 2); }
+    if (bo >= 32u) { w0 = w1; w1 = w2; w2 = w3; widx++; bo -= 32u; w3 = ld(widx + 3); }
+    if (bo >= 32u) { w0 = w1; w1 = w2; w2 = w3; widx++; bo -= 32u; w3 = ld(widx + 3); }
   }
 };
 
@@ -257,15 +258,35 @@ DEFL_DEV void lane_redo(const uint16_t* lit, const uint16_t* dist, const uint32_
 // SYM = uint8_t: plain bytes.  SYM = uint16_t (split decode of one large stream, split_decode.cuh): the
 // chunk does not know the 32 KiB before its start, so a byte copied from there becomes the marker
 // 0x8000 | k (k = index into that window) and markers are copied around like bytes; `hist` = 32768 then.
+//
+// Up to 32 tokens per batch, ONE TOKEN PER LANE (profiles/r01_v3_*: the earlier one-byte-per-lane walk cost
+// 2.7 warp instructions per byte, half of the kernel).  The batch is assembled in a shared-memory stage laid
+// out with the same 4-byte phase as its place in dst, then stored as aligned words:
+//   1. lanes with a literal token, or a short match whose source lies wholly before the batch, fill their
+//      own symbols: the source is read as aligned 32-bit words and funnel-shifted into place;
+//   2. long matches that source before the batch are copied by the whole warp, one after another;
+//   3. matches that read symbols of this very batch follow in token order, by the whole warp, from the stage;
+//   4. the stage goes to dst as aligned words (symbols at the ragged ends singly).
+template <typename SYM> struct SymWord;
+template <> struct SymWord<uint8_t>  { static constexpr uint32_t kPer = 4, kShift = 2, kBits = 8,  kMask = 0xFFu; };
+template <> struct SymWord<uint16_t> { static constexpr uint32_t kPer = 2, kShift = 1, kBits = 16, kMask = 0xFFFFu; };
+constexpr uint32_t kLaneWords = 4;      // a lane copies matches of up to this many words' worth of symbols itself
+
 template <typename SYM>
-DEFL_DEV uint32_t resolve_tokens(uint16_t* stage, int lane, const uint32_t* toks, uint32_t count, SYM* dst0,
+DEFL_DEV uint32_t resolve_tokens(uint16_t* stage_mem, int lane, const uint32_t* toks, uint32_t count, SYM* dst0,
                                  uint32_t cap, uint32_t& P, uint32_t hist) {
-  const unsigned le = simt::lanemask_le();
+  using SW = SymWord<SYM>;
+  constexpr uint32_t kPer = SW::kPer;
+  constexpr uint32_t kRoom = (uint32_t)(kStageV3 * sizeof(uint16_t) / sizeof(SYM)) - kPer;   // symbols per batch
+  SYM* const      st  = reinterpret_cast<SYM*>(stage_mem);
+  uint32_t* const stw = reinterpret_cast<uint32_t*>(stage_mem);
   uint32_t h = 0;
+  uint32_t nxt = (uint32_t)lane < count ? simt::ld_tok(toks + lane) : 0u;
 #pragma unroll 1
   while (h < count) {
     uint32_t n = count - h < 32u ? count - h : 32u;
-    uint32_t tok = (uint32_t)lane < n ? simt::ld_tok(toks + h + lane) : 0u;
+    uint32_t tok = nxt;
+    nxt = h + 32u + (uint32_t)lane < count ? simt::ld_tok(toks + h + 32u + lane) : 0u;    // lands during this batch
     uint32_t olen = (tok >> 31) ? (tok & 511u) : ((tok >> 24) & 7u);
 
     uint32_t inc = olen;                                   // inclusive prefix sum of output lengths
@@ -274,52 +295,89 @@ DEFL_DEV uint32_t resolve_tokens(uint16_t* stage, int lane, const uint32_t* toks
       const uint32_t t = simt::shfl_up(kFull, inc, d);
       if (lane >= d) inc += t;
     }
-    const uint32_t o = inc - olen;                         // this token's first byte inside the batch
+    const uint32_t o  = inc - olen;                        // this token's first symbol inside the batch
     const uint32_t d1 = (tok >> 9) & 0x7FFFu;              // distance - 1
     const bool bad_dist = (tok >> 31) && d1 >= P + o + hist;
     const bool bad_full = olen != 0u && inc > cap - P;
-    const bool nofit    = inc > (uint32_t)kStageV3;
+    const bool nofit    = inc > kRoom;
     // all three are monotone or first-hit: keep the tokens before the first stop
     const unsigned stop = simt::ballot(kFull, bad_dist || bad_full || nofit || (uint32_t)lane >= n);
     const uint32_t keep = stop ? (uint32_t)simt::ffs(stop) - 1u : 32u;
     if (keep == 0u) {
-      // token 0 of the batch fails (one token always fits the stage: <= 258 bytes)
+      // token 0 of the batch fails (one token always fits the stage: <= 258 symbols)
       const uint32_t bd = simt::shfl(kFull, (uint32_t)bad_dist, 0);
       return bd ? R_DISTANCE : R_OUTPUT_FULL;
     }
+    const bool short_batch = keep != 32u && h + keep < count;
     n = keep;
     if ((uint32_t)lane >= n) { tok = 0u; olen = 0u; }
-    const uint32_t B = simt::shfl(kFull, inc, (int)n - 1);
-    SYM*           dst = dst0 + P;
+    const uint32_t B  = simt::shfl(kFull, inc, (int)n - 1);
+    SYM* const     dst = dst0 + P;
+    const uint32_t a0 = (uint32_t)(((uintptr_t)dst & 3u) / sizeof(SYM));      // stage index of the batch's symbol 0
+    const bool     is_match = (tok >> 31) != 0u;
+    const bool     dep  = is_match && (d1 + 1u < o + olen);                   // reads symbols of this batch
+    const bool     wide = is_match && !dep && olen > kLaneWords * kPer;       // phase 2
 
-    const bool dep = (tok >> 31) && (d1 + 1u < o + olen);
-    if (dep) tok |= kTokIsDep;
-
-    const bool     valid = olen != 0u;
-    const uint32_t ks = o >> 5, kb = 1u << (o & 31u);
-    simt::syncwarp(kFull);
-#pragma unroll 1
-    for (uint32_t base = 0; base < B; base += 128u) {
-      uint32_t val[4];
-      bool     have[4];
+    simt::syncwarp(kFull);            // the previous batch's stage has been stored
+    // ---- 1. every lane fills its own short token
+    if (!is_match) {
+      if (olen) st[a0 + o] = (SYM)(tok & 255u);
+      if (olen > 1u) st[a0 + o + 1u] = (SYM)((tok >> 8) & 255u);
+    } else if (!dep && !wide) {
+      const int32_t   g0 = (int32_t)o - (int32_t)(d1 + 1u);                   // first source symbol, relative to dst (< 0)
+      const uintptr_t sa = (uintptr_t)(dst + g0);
+      const uint32_t* wp = reinterpret_cast<const uint32_t*>(sa & ~(uintptr_t)3);
+      const uint32_t  sh = (uint32_t)(sa & 3u) * 8u;
+      const uint32_t  last_word = (uint32_t)(((sa & 3u) + olen * sizeof(SYM) - 1u) >> 2);   // words the source spans - 1
+      // 16-bit symbols: what lies before the chunk is never read (those symbols become markers below)
+      const uint32_t* const wmin = sizeof(SYM) == 2 ? reinterpret_cast<const uint32_t*>((uintptr_t)dst0 & ~(uintptr_t)3) : nullptr;
+      // all the words first (independent loads in flight together), then shift and store
+      uint32_t w[kLaneWords + 1];
 #pragma unroll
-      for (int u = 0; u < 4; u++) {
-        const uint32_t rb = base + 32u * (uint32_t)u;
-        have[u] = false;
-        val[u] = 0;
-        if (rb < B) {                                      // uniform
-          const uint32_t k = rb >> 5;
-          const uint32_t before = (uint32_t)simt::popc(simt::ballot(kFull, valid && ks < k));
-          const uint32_t starts = simt::reduce_or(kFull, (valid && ks == k) ? kb : 0u);
-          const int      i  = (int)((before + (uint32_t)simt::popc(starts & le) - 1u) & 31u);
-          const uint32_t t  = simt::shfl(kFull, tok, i);
-          const uint32_t oi = simt::shfl(kFull, o, i);
-          const uint32_t j  = rb + (uint32_t)lane;
-          if (j < B) {
-            if (!(t >> 31)) {
-              val[u] = (t >> (8u * (j - oi))) & 255u;
-              have[u] = true;
-            } else if (!(t & kTokIsDep)) {
+      for (uint32_t i = 0; i <= kLaneWords; i++)
+        w[i] = (i <= last_word && (sizeof(SYM) == 1 || wp + i >= wmin)) ? simt::ld_outw(wp + i) : 0u;
+#pragma unroll
+      for (uint32_t wi = 0; wi < kLaneWords; wi++) {
+        const uint32_t k = wi * kPer;
+        const uint32_t v = simt::funnel_r(w[wi], w[wi + 1], sh);
+#pragma unroll
+        for (uint32_t i = 0; i < kPer; i++) {
+          if (k + i < olen) {
+            uint32_t x = (v >> (i * SW::kBits)) & SW::kMask;
+            if (sizeof(SYM) == 2) {
+              const int32_t gi = (int32_t)P + g0 + (int32_t)(k + i);
+              if (gi < 0) x = 0x8000u | (uint32_t)(gi + 32768);
+            }
+            st[a0 + o + k + i] = (SYM)x;
+          }
+        }
+      }
+    }
+    // ---- 2. long matches from before the batch: one symbol per lane across all of them, 128 per step
+    if (simt::any(kFull, wide)) {
+      const unsigned le = simt::lanemask_le();
+      const uint32_t p_lo = simt::reduce_min(kFull, wide ? o : 0xFFFFFFFFu);
+      const uint32_t p_hi = simt::reduce_max(kFull, wide ? o + olen : 0u);
+      const bool     valid = olen != 0u;
+      const uint32_t ks = o >> 5, kb = 1u << (o & 31u);
+#pragma unroll 1
+      for (uint32_t base = p_lo & ~31u; base < p_hi; base += 128u) {
+        uint32_t val[4];
+        bool     have[4];
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+          const uint32_t rb = base + 32u * (uint32_t)u;
+          have[u] = false;
+          val[u] = 0;
+          if (rb < p_hi) {                                   // uniform
+            const uint32_t k = rb >> 5;
+            const uint32_t before = (uint32_t)simt::popc(simt::ballot(kFull, valid && ks < k));
+            const uint32_t starts = simt::reduce_or(kFull, (valid && ks == k) ? kb : 0u);
+            const int      i  = (int)((before + (uint32_t)simt::popc(starts & le) - 1u) & 31u);
+            const uint32_t t  = simt::shfl(kFull, tok, i);
+            const uint32_t wd = simt::shfl(kFull, (uint32_t)wide, i);
+            const uint32_t j  = rb + (uint32_t)lane;
+            if (j < B && wd) {
               const int32_t back = (int32_t)j - (int32_t)(((t >> 9) & 0x7FFFu) + 1u);
               if (sizeof(SYM) == 2 && (int32_t)P + back < 0) val[u] = 0x8000u | (uint32_t)((int32_t)P + back + 32768);
               else val[u] = simt::ld_out(dst + back);
@@ -327,18 +385,12 @@ DEFL_DEV uint32_t resolve_tokens(uint16_t* stage, int lane, const uint32_t* toks
             }
           }
         }
-      }
 #pragma unroll
-      for (int u = 0; u < 4; u++) {
-        const uint32_t j = base + 32u * (uint32_t)u + (uint32_t)lane;
-        if (have[u]) {
-          stage[j] = (uint16_t)val[u];
-          dst[j] = (SYM)val[u];
-        }
+        for (int u = 0; u < 4; u++)
+          if (have[u]) st[a0 + base + 32u * (uint32_t)u + (uint32_t)lane] = (SYM)val[u];
       }
     }
-
-    // matches that read bytes of this very batch: in token order, each by the whole warp
+    // ---- 3. matches that read symbols of this very batch: in token order, each by the whole warp
     unsigned depmask = simt::ballot(kFull, dep);
 #pragma unroll 1
     while (depmask) {
@@ -348,21 +400,54 @@ DEFL_DEV uint32_t resolve_tokens(uint16_t* stage, int lane, const uint32_t* toks
       const uint32_t oi = simt::shfl(kFull, o, i);
       const uint32_t len = t & 511u, dist = ((t >> 9) & 0x7FFFu) + 1u;
       simt::syncwarp(kFull);
-      for (uint32_t r = (uint32_t)lane; r < len; r += 32u) {
-        const uint32_t sr = dist < len ? r % dist : r;     // a period shorter than the match repeats
-        const int32_t  so = (int32_t)oi - (int32_t)dist + (int32_t)sr;
-        uint32_t v;
-        if (so >= 0) v = stage[so];
-        else if (sizeof(SYM) == 2 && (int32_t)P + so < 0) v = 0x8000u | (uint32_t)((int32_t)P + so + 32768);
-        else v = simt::ld_out(dst + so);
-        stage[oi + r] = (uint16_t)v;
-        dst[oi + r] = (SYM)v;
+      if (dist >= 32u || dist >= len) {
+        // no lane reads what another writes in the same step; a later step may (dist < len)
+        for (uint32_t r0 = 0; r0 < len; r0 += 32u) {
+          const uint32_t r = r0 + (uint32_t)lane;
+          if (r < len) {
+            const int32_t so = (int32_t)oi - (int32_t)dist + (int32_t)r;
+            uint32_t v;
+            if (so >= 0) v = st[a0 + so];
+            else if (sizeof(SYM) == 2 && (int32_t)P + so < 0) v = 0x8000u | (uint32_t)((int32_t)P + so + 32768);
+            else v = simt::ld_out(dst + so);
+            st[a0 + oi + r] = (SYM)v;
+          }
+          if (dist < len) simt::syncwarp(kFull);
+        }
+      } else {
+        // a period shorter than a step: every symbol is one of the `dist` symbols before the match
+        for (uint32_t r = (uint32_t)lane; r < len; r += 32u) {
+          const int32_t so = (int32_t)oi - (int32_t)dist + (int32_t)(r % dist);
+          uint32_t v;
+          if (so >= 0) v = st[a0 + so];
+          else if (sizeof(SYM) == 2 && (int32_t)P + so < 0) v = 0x8000u | (uint32_t)((int32_t)P + so + 32768);
+          else v = simt::ld_out(dst + so);
+          st[a0 + oi + r] = (SYM)v;
+        }
       }
     }
     simt::syncwarp(kFull);
+    // ---- 4. stage -> dst: aligned words, the ragged ends symbol by symbol
+    {
+      const uint32_t s_end = a0 + B;
+      const uint32_t w_lo  = (a0 + kPer - 1u) >> SW::kShift;
+      const uint32_t w_hi  = s_end >> SW::kShift;
+      uint32_t* const gw = reinterpret_cast<uint32_t*>((uintptr_t)dst & ~(uintptr_t)3);     // word of stage word 0
+      if (w_hi > w_lo) {
+        for (uint32_t w = w_lo + (uint32_t)lane; w < w_hi; w += 32u) gw[w] = stw[w];
+        const uint32_t head = (w_lo << SW::kShift) - a0;                    // < kPer
+        const uint32_t tail = s_end - (w_hi << SW::kShift);                 // < kPer
+        if ((uint32_t)lane < head) dst[lane] = st[a0 + lane];
+        if ((uint32_t)lane < tail) dst[B - tail + lane] = st[s_end - tail + lane];
+      } else {
+        if ((uint32_t)lane < B) dst[lane] = st[a0 + lane];                  // B < 2 * kPer here
+      }
+    }
     P += B;
     h += n;
+    if (short_batch) nxt = h + (uint32_t)lane < count ? simt::ld_tok(toks + h + lane) : 0u;
   }
+  simt::syncwarp(kFull);
   return R_NONE;
 }
 
@@ -427,6 +512,15 @@ DEFL_DEV uint32_t decode_window(WarpSmem& sm, const WarpScratch& sc, int lane, c
     if (!simt::any(kFull, need)) break;
     if (need) lane_redo(sm.lit, sm.dist, words, wend, bw, start, limit, endr, fix, cps, pland, tj);
     simt::syncwarp(kFull);
+  }
+
+  // a lane's fix-up tokens move in front of its true speculative tokens when the discarded ones left room:
+  // one run of tokens per lane for the resolver instead of two
+  if (active && tj.nf != 0u && tj.nf <= tj.m && tj.n > tj.m) {
+    uint32_t* to = seg + (tj.m - tj.nf);
+    for (uint32_t i = 0; i < tj.nf; i++) to[i] = simt::ld_tok(fix + i);
+    tj.m -= tj.nf;
+    tj.nf = 0;
   }
 
   // the first lane whose true trajectory stopped ends the window; without one, the last active lane does

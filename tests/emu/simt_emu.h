@@ -110,6 +110,7 @@ inline long long ticks() { return 0; }
 inline uint32_t ld_out8(const uint8_t* p) { return *(const volatile uint8_t*)p; }
 inline uint32_t ld_out(const uint8_t* p) { return *(const volatile uint8_t*)p; }
 inline uint32_t ld_out(const uint16_t* p) { return *(const volatile uint16_t*)p; }
+inline uint32_t ld_outw(const uint32_t* p) { return *(const volatile uint32_t*)p; }
 inline bool any(unsigned mk, bool p) { return ballot(mk, p) != 0u; }
 inline int clz(uint32_t v) { return v ? __builtin_clz(v) : 32; }
 inline uint32_t reduce_add(unsigned, uint32_t v) {
@@ -117,6 +118,22 @@ inline uint32_t reduce_add(unsigned, uint32_t v) {
   barrier();
   uint32_t r = 0;
   for (int i = 0; i < t_group->G; i++) r += t_group->xchg[i];
+  barrier();
+  return r;
+}
+inline uint32_t reduce_min(unsigned, uint32_t v) {
+  t_group->xchg[t_lane] = v;
+  barrier();
+  uint32_t r = 0xFFFFFFFFu;
+  for (int i = 0; i < t_group->G; i++) r = t_group->xchg[i] < r ? t_group->xchg[i] : r;
+  barrier();
+  return r;
+}
+inline uint32_t reduce_max(unsigned, uint32_t v) {
+  t_group->xchg[t_lane] = v;
+  barrier();
+  uint32_t r = 0;
+  for (int i = 0; i < t_group->G; i++) r = t_group->xchg[i] > r ? t_group->xchg[i] : r;
   barrier();
   return r;
 }
