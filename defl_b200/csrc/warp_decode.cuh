@@ -61,15 +61,24 @@ struct SubReader {
   uint32_t        bo;
 
   DEFL_DEV uint32_t ld(uint32_t i) const { return i < wend ? simt::ld_in32(w + i) : 0u; }
+  // The lanes of an SM stream through more 128-byte lines than its L1 holds, and a line's first word comes
+  // from HBM: ask for the line two ahead (into L2) whenever the reader enters a new one.
+  DEFL_DEV void ahead(uint32_t i) const {
+    if ((i & 31u) == 0u && i + 64u < wend) simt::prefetch_l2(w + i + 64u);
+  }
   DEFL_DEV void seek(uint32_t word, uint32_t bit) {
     widx = word + (bit >> 5);
     bo   = bit & 31u;
     w0 = ld(widx); w1 = ld(widx + 1); w2 = ld(widx + 2); w3 = ld(widx + 3);
+    if (widx + 32u < wend) simt::prefetch_l2(w + widx + 32u);
+    if (widx + 64u < wend) simt::prefetch_l2(w + widx + 64u);
   }
   DEFL_DEV void consume(uint32_t n) {     // n <= 48, bo < 32 on entry
     bo += n;
-    if (bo >= 32u) { w0 = w1; w1 = w2; w2 = w3; widx++; bo -= 32u; w3 = ld(widx + 3); }
-    if (bo >= 32u) { w0 = w1; w1 = w2; w2 = w3; widx++; bo -= 32u; w3 = ld(widx + 3); }
+    // a loop, not two ifs: if-converted, the second step's moves wait for the word the first step has only
+    // just asked for, taken or not (13 % of all stall samples in profiles/r01_v3b_*); a real branch does not
+#pragma unroll 1
+    while (bo >= 32u) { w0 = w1; w1 = w2; w2 = w3; widx++; bo -= 32u; w3 = ld(widx + 3); ahead(widx + 3u); }
   }
 };
 
