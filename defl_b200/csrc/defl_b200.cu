@@ -859,6 +859,19 @@ UNZ_EXPORT int infl_gather_device(const void* const* d_seg_src, const uint64_t* 
   return UNZ_OK;
 }
 
+UNZ_EXPORT int infl_batch_partition(const infl_batch_item_t* items, size_t n, int nparts, uint32_t* part_of,
+                                    uint64_t* shard_bytes) {
+  if ((!items && n) || (!part_of && n) || nparts < 1 || n > 0xFFFFFFFFull) return fail("infl_batch_partition: bad arguments");
+  std::vector<std::vector<uint32_t>> parts;
+  partition_lpt(items, n, nparts, parts);
+  for (int g = 0; g < nparts; g++) {
+    uint64_t b = 0;
+    for (uint32_t i : parts[g]) { part_of[i] = (uint32_t)g; b += items[i].srclen + items[i].dstlen; }
+    if (shard_bytes) shard_bytes[g] = b;
+  }
+  return UNZ_OK;
+}
+
 UNZ_EXPORT int infl_buf_batch(const infl_batch_item_t* items, size_t n, int flags, infl_batch_result_t* results) {
   if (n == 0) return UNZ_OK;
   if (!items || !results) return fail("null argument");

@@ -30,7 +30,7 @@ constexpr uint32_t kSubMin    = 512;
 constexpr uint32_t kCpBits    = 128;                  // checkpoint spacing
 constexpr uint32_t kCpPerLane = kSubMax / kCpBits;
 constexpr uint32_t kSpecCap   = 1024;                 // tokens per lane per window (speculative pass)
-constexpr uint32_t kFixCap    = 256;                  // tokens per lane per window (fix-up pass)
+constexpr uint32_t kFixCap    = 1024;                 // tokens per lane per window (fix-up pass)
 constexpr size_t   kWarpScratchBytes = 32u * (kSpecCap + kFixCap) * 4u + 32u * kCpPerLane * 2u;
 static_assert(kWarpScratchBytes % 16 == 0, "scratch slices stay 16-byte aligned");
 

@@ -96,6 +96,16 @@ UNZ_EXPORT int infl_gather_device(const void *const *d_seg_src, const uint64_t *
                                   const uint64_t *d_seg_dst_off, size_t nseg, void *d_out,
                                   void *cuda_stream);
 
+/* ---- sharding (host only, no device needed) ------------------------------------------- */
+
+/* Byte-balanced partition of n independent streams into nparts shards: greedy longest-processing-time
+ * on srclen + dstlen, largest first.  part_of[i] = shard of stream i.  It is what INFL_BATCH_ALL_GPUS
+ * uses inside one process and what one-process-per-GPU callers use to pick their share (rank r decodes
+ * the streams with part_of[i] == r); there is no exchange between shards.  shard_bytes (optional,
+ * nparts entries) receives each shard's srclen + dstlen total.  Returns UNZ_OK / UNZ_ERR. */
+UNZ_EXPORT int infl_batch_partition(const infl_batch_item_t *items, size_t n, int nparts,
+                                    uint32_t *part_of, uint64_t *shard_bytes);
+
 /* ---- engine control ------------------------------------------------------------------ */
 UNZ_EXPORT int         infl_device_count(void);
 UNZ_EXPORT const char *infl_last_error(void);       /* thread-local, "" when none */
