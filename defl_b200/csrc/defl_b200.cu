@@ -279,18 +279,29 @@ uint32_t env_u32(const char* name, uint32_t dflt, uint32_t lo, uint32_t hi) {
 std::atomic<uint64_t> g_split_decodes{0};
 
 struct SplitBufs {
-  DevBuf d_found, d_cand, d_jobs, d_outs, d_outs2, d_sym, d_off, d_partial, d_wbuf, d_tok;
+  DevBuf d_found, d_cand, d_jobs, d_outs, d_outs2, d_sym, d_off, d_partial, d_wbuf, d_tok, d_streams, d_peek, d_at;
 };
 SplitBufs g_split[kMaxDevices];
 
-// Returns UNZ_OK with *res filled when the split path decoded the stream, UNZ_NOOP when the stream has to go
-// through the one-warp decoder instead (too few block starts, any failure: that path defines error behaviour),
-// UNZ_ERR when the engine itself failed.  d_src / d_dst are device pointers; d_ws is the token scratch.
-int split_decode_device(Engine* E, const uint8_t* d_src, uint64_t srclen, uint8_t* d_dst, uint64_t dstlen, int flags,
-                        void* d_ws, cudaStream_t st, infl_batch_result_t* res) {
+struct SplitInput {          // one stream handed to the split decoder: device pointers
+  const uint8_t* d_src;
+  uint64_t       srclen;
+  uint8_t*       d_dst;
+  uint64_t       dstlen;
+};
+
+// Split decode of MANY streams at once (every kernel works on all of them: see split_decode.cuh).
+// status[i] = UNZ_OK with res[i] filled when stream i was decoded here, UNZ_NOOP when it has to go through
+// the one-warp decoder instead (too few block starts, any failure: that path defines error behaviour).
+// Returns UNZ_ERR only when the engine itself failed.  d_ws is the token scratch of the batch engine.
+int split_decode_many(Engine* E, const SplitInput* in, size_t nin, int flags, void* d_ws, cudaStream_t st,
+                      infl_batch_result_t* res, int* status) {
   using namespace defl;
   SplitBufs& SB = g_split[E->dev];
   const bool zlib = (flags & 0xFF) == INFL_ZLIB;
+  const uint32_t ns = (uint32_t)nin;
+  for (uint32_t i = 0; i < ns; i++) status[i] = UNZ_NOOP;
+  if (!ns) return UNZ_OK;
   // DEFL_SPLIT_TRACE=1: per-phase wall times on stderr (adds a stream synchronise per phase)
   static const bool trace = std::getenv("DEFL_SPLIT_TRACE") != nullptr;
   auto tnow = [] { return std::chrono::steady_clock::now(); };
@@ -302,59 +313,108 @@ int split_decode_device(Engine* E, const uint8_t* d_src, uint64_t srclen, uint8_
     std::fprintf(stderr, "[split] %-28s %8.3f ms\n", what, std::chrono::duration<double, std::milli>(t - tprev).count());
     tprev = t;
   };
-  uint32_t   body = 0;
-  if (zlib) {
-    uint8_t h2[2];
-    CU_TRY(cudaMemcpyAsync(h2, d_src, 2, cudaMemcpyDeviceToHost, st), "D2H zlib header");
-    CU_TRY(cudaStreamSynchronize(st), "D2H zlib header");
-    if ((h2[0] & 15) != 8 || (h2[0] >> 4) > 7 || ((h2[0] << 8) + h2[1]) % 31 != 0 || (h2[1] & 0x20)) return UNZ_NOOP;
-    body = 2;
-  }
+  static const uint32_t granule = env_u32("DEFL_SPLIT_GRANULE", 32768u, 4096u, 1u << 24);
+  static const uint64_t min_gap = (uint64_t)env_u32("DEFL_SPLIT_GAP", 40960u, 0u, 1u << 28) * 8u;   // bits
+  static const uint32_t tok_per_byte = env_u32("DEFL_SPLIT_TOKENS_PER_BYTE", 2u, 0u, 32u);
+
   int grid_warps = 0;
   if (warp_kernel_grid(E->sms, &grid_warps) != UNZ_OK) return UNZ_ERR;      // CTAs of kWarpsPerCta warps
   auto* ticket  = static_cast<unsigned int*>(d_ws);
   auto* scratch = static_cast<unsigned char*>(d_ws) + kWsHeader;
   const size_t smem = sizeof(WarpSmem) * kWarpsPerCta;
 
+  std::vector<SplitStreamDesc> sd(ns);
+  std::vector<char> alive(ns, 1);
+  for (uint32_t i = 0; i < ns; i++) {
+    std::memset(&sd[i], 0, sizeof(sd[i]));
+    sd[i].src = in[i].d_src; sd[i].dst = in[i].d_dst; sd[i].srclen = in[i].srclen;
+    if (in[i].srclen > 0xFFFFFFFFull || in[i].dstlen > 0xFFFFFFFFull || in[i].srclen < 64) alive[i] = 0;
+  }
+  if (SB.d_streams.reserve((size_t)ns * sizeof(SplitStreamDesc)) || SB.d_peek.reserve((size_t)ns * 4) || SB.d_at.reserve((size_t)ns * 8))
+    return UNZ_ERR;
+  auto* d_sd = static_cast<SplitStreamDesc*>(SB.d_streams.p);
+  auto upload_streams = [&]() -> int {
+    CU_TRY(cudaMemcpyAsync(d_sd, sd.data(), (size_t)ns * sizeof(SplitStreamDesc), cudaMemcpyHostToDevice, st), "H2D stream table");
+    return UNZ_OK;
+  };
+
+  // ---- zlib headers
+  if (zlib) {
+    if (upload_streams() != UNZ_OK) return UNZ_ERR;
+    std::vector<uint8_t> h2((size_t)ns * 2);
+    split_peek_kernel<<<(ns + 127) / 128, 128, 0, st>>>(d_sd, ns, nullptr, 2u, static_cast<uint8_t*>(SB.d_peek.p));
+    CU_TRY(cudaGetLastError(), "split_peek_kernel launch");
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+    CU_TRY(cudaMemcpyAsync(h2.data(), SB.d_peek.p, h2.size(), cudaMemcpyDeviceToHost, st), "D2H zlib headers");
+    CU_TRY(cudaStreamSynchronize(st), "D2H zlib headers");
+    for (uint32_t i = 0; i < ns; i++) {
+      const uint8_t c0 = h2[2 * i], c1 = h2[2 * i + 1];
+      if ((c0 & 15) != 8 || (c0 >> 4) > 7 || ((c0 << 8) + c1) % 31 != 0 || (c1 & 0x20)) alive[i] = 0;
+      sd[i].body = 2;
+    }
+  }
+
   // ---- F: block starts
-  static const uint32_t granule = env_u32("DEFL_SPLIT_GRANULE", 32768u, 4096u, 1u << 24);
-  static const uint64_t min_gap = (uint64_t)env_u32("DEFL_SPLIT_GAP", 40960u, 0u, 1u << 28) * 8u;   // bits
-  const uint32_t ngran = (uint32_t)((srclen - body + granule - 1) / granule);
-  if (SB.d_found.reserve((size_t)ngran * 8)) return UNZ_ERR;
-  find_block_starts_kernel<kWarpsPerCta><<<(ngran + kWarpsPerCta - 1) / kWarpsPerCta, kWarpsPerCta * 32, 0, st>>>(
-      d_src, (uint32_t)srclen, body, ngran, granule, static_cast<uint64_t*>(SB.d_found.p));
+  uint32_t ngran_total = 0;
+  for (uint32_t i = 0; i < ns; i++) {
+    sd[i].gran_base = ngran_total;
+    sd[i].ngran = alive[i] ? (uint32_t)((in[i].srclen - sd[i].body + granule - 1) / granule) : 0u;
+    ngran_total += sd[i].ngran;
+  }
+  if (!ngran_total) return UNZ_OK;
+  if (SB.d_found.reserve((size_t)ngran_total * 8) || upload_streams() != UNZ_OK) return UNZ_ERR;
+  find_block_starts_kernel<kWarpsPerCta><<<(ngran_total + kWarpsPerCta - 1) / kWarpsPerCta, kWarpsPerCta * 32, 0, st>>>(
+      d_sd, ns, ngran_total, granule, static_cast<uint64_t*>(SB.d_found.p));
   CU_TRY(cudaGetLastError(), "find_block_starts_kernel launch");
   g_launches.fetch_add(1, std::memory_order_relaxed);
-  std::vector<uint64_t> found(ngran);
-  CU_TRY(cudaMemcpyAsync(found.data(), SB.d_found.p, (size_t)ngran * 8, cudaMemcpyDeviceToHost, st), "D2H block starts");
+  std::vector<uint64_t> found(ngran_total);
+  CU_TRY(cudaMemcpyAsync(found.data(), SB.d_found.p, (size_t)ngran_total * 8, cudaMemcpyDeviceToHost, st), "D2H block starts");
   CU_TRY(cudaStreamSynchronize(st), "find_block_starts_kernel");
   mark("F find_block_starts");
   std::vector<uint64_t> cand;
-  cand.push_back((uint64_t)body * 8);
-  for (uint64_t f : found)
-    if (f != kNoCandidate && f >= cand.back() + min_gap && f > cand.back()) cand.push_back(f);
+  for (uint32_t i = 0; i < ns; i++) {
+    sd[i].cand_base = (uint32_t)cand.size();
+    if (!alive[i]) continue;
+    cand.push_back((uint64_t)sd[i].body * 8);
+    for (uint32_t g = 0; g < sd[i].ngran; g++) {
+      const uint64_t f = found[sd[i].gran_base + g];
+      if (f != kNoCandidate && f >= cand.back() + min_gap && f > cand.back()) cand.push_back(f);
+    }
+    sd[i].ncand = (uint32_t)cand.size() - sd[i].cand_base;
+    if (sd[i].ncand < 8) { alive[i] = 0; cand.resize(sd[i].cand_base); sd[i].ncand = 0; }
+  }
   const uint32_t ncand = (uint32_t)cand.size();
-  if (ncand < 8) return UNZ_NOOP;
+  if (!ncand) return UNZ_OK;
 
-  // ---- A: every candidate counts its chunk
-  // The count pass keeps each chunk's tokens (tok_per_byte tokens of budget per compressed byte, regions
-  // laid out by compressed position) so that the decode pass only has to turn them into bytes.
-  static const uint32_t tok_per_byte = env_u32("DEFL_SPLIT_TOKENS_PER_BYTE", 2u, 0u, 32u);
+  // ---- A: every candidate counts its chunk.  The count pass keeps each chunk's tokens (tok_per_byte tokens of
+  // budget per compressed byte, regions laid out by compressed position) so that the decode pass only has to
+  // turn them into bytes.
+  uint64_t tok_total = 0;
+  for (uint32_t i = 0; i < ns; i++) {
+    sd[i].tok_base = tok_total;
+    if (alive[i]) tok_total += (uint64_t)tok_per_byte * in[i].srclen + 16;
+  }
   uint32_t* d_tok = nullptr;
   if (tok_per_byte) {
-    if (SB.d_tok.reserve_exact((size_t)tok_per_byte * srclen * 4 + 64) == UNZ_OK) d_tok = static_cast<uint32_t*>(SB.d_tok.p);
-    else cudaGetLastError();       // no room for it: the decode pass decodes again, as before
+    if (SB.d_tok.reserve_exact((size_t)tok_total * 4 + 64) == UNZ_OK) d_tok = static_cast<uint32_t*>(SB.d_tok.p);
+    else cudaGetLastError();       // no room for it: the decode pass decodes again
   }
   std::vector<SplitJob> jobs(ncand);
-  for (uint32_t i = 0; i < ncand; i++) {
-    const uint64_t b0 = cand[i] >> 3, b1 = i + 1 < ncand ? cand[i + 1] >> 3 : srclen;
-    jobs[i].cand = i; jobs[i].cap = 0; jobs[i].out_off = 0;
-    jobs[i].tok_off = (uint64_t)tok_per_byte * b0;
-    jobs[i].tok_cap = (uint32_t)std::min<uint64_t>((uint64_t)tok_per_byte * (b1 - b0), 0xFFFFFFF0ull);
-    jobs[i].ntok = kNoTokens;
+  {
+    uint32_t j = 0;
+    for (uint32_t i = 0; i < ns; i++)
+      for (uint32_t k = 0; k < sd[i].ncand; k++, j++) {
+        const uint64_t* c = cand.data() + sd[i].cand_base;
+        const uint64_t b0 = c[k] >> 3, b1 = k + 1 < sd[i].ncand ? c[k + 1] >> 3 : in[i].srclen;
+        jobs[j].stream = i; jobs[j].pad = 0; jobs[j].cand = k; jobs[j].cap = 0; jobs[j].out_off = 0;
+        jobs[j].tok_off = sd[i].tok_base + (uint64_t)tok_per_byte * b0;
+        jobs[j].tok_cap = (uint32_t)std::min<uint64_t>((uint64_t)tok_per_byte * (b1 - b0), 0xFFFFFFF0ull);
+        jobs[j].ntok = kNoTokens;
+      }
   }
   if (SB.d_cand.reserve((size_t)ncand * 8) || SB.d_jobs.reserve((size_t)ncand * sizeof(SplitJob)) ||
-      SB.d_outs.reserve((size_t)ncand * sizeof(SplitChunkOut)) || SB.d_outs2.reserve((size_t)ncand * sizeof(SplitChunkOut)))
+      SB.d_outs.reserve((size_t)ncand * sizeof(SplitChunkOut)) || SB.d_outs2.reserve((size_t)ncand * sizeof(SplitChunkOut)) ||
+      upload_streams() != UNZ_OK)
     return UNZ_ERR;
   CU_TRY(cudaMemcpyAsync(SB.d_cand.p, cand.data(), (size_t)ncand * 8, cudaMemcpyHostToDevice, st), "H2D candidates");
   CU_TRY(cudaMemcpyAsync(SB.d_jobs.p, jobs.data(), (size_t)ncand * sizeof(SplitJob), cudaMemcpyHostToDevice, st), "H2D jobs");
@@ -369,11 +429,11 @@ int split_decode_device(Engine* E, const uint8_t* d_src, uint64_t srclen, uint8_
     CU_TRY(cudaMemsetAsync(ticket, 0, sizeof(unsigned int), st), "cudaMemsetAsync(ticket)");
     if (count)
       split_chunk_kernel<true, kWarpsPerCta><<<grid, kWarpsPerCta * 32, smem, st>>>(
-          d_src, (uint32_t)srclen, static_cast<uint64_t*>(SB.d_cand.p), ncand, static_cast<SplitJob*>(SB.d_jobs.p), njobs,
+          d_sd, static_cast<uint64_t*>(SB.d_cand.p), static_cast<SplitJob*>(SB.d_jobs.p), njobs,
           sym, static_cast<SplitChunkOut*>(SB.d_outs.p), ticket, scratch, d_tok);
     else
       split_chunk_kernel<false, kWarpsPerCta><<<grid, kWarpsPerCta * 32, smem, st>>>(
-          d_src, (uint32_t)srclen, static_cast<uint64_t*>(SB.d_cand.p), ncand, static_cast<SplitJob*>(SB.d_jobs.p), njobs,
+          d_sd, static_cast<uint64_t*>(SB.d_cand.p), static_cast<SplitJob*>(SB.d_jobs.p), njobs,
           sym, static_cast<SplitChunkOut*>(SB.d_outs2.p), ticket, scratch, d_tok);
     CU_TRY(cudaGetLastError(), "split_chunk_kernel launch");
     g_launches.fetch_add(1, std::memory_order_relaxed);
@@ -385,108 +445,169 @@ int split_decode_device(Engine* E, const uint8_t* d_src, uint64_t srclen, uint8_
   CU_TRY(cudaStreamSynchronize(st), "split_chunk_kernel (count)");
   mark("A count pass");
 
-  // ---- the chain of true chunks, from the stream's first block to its final block
-  std::vector<uint32_t> chain;
-  std::vector<uint64_t> off;
-  uint64_t total = 0, end_bit = 0;
-  for (uint32_t i = 0;;) {
-    const SplitChunkOut& o = outs[i];
-    if ((o.status & 0xFF) == CH_FAIL) return UNZ_NOOP;
-    chain.push_back(i);
+  // ---- per stream, the chain of true chunks from its first block to its final block
+  struct ChainItem { uint32_t stream, cand; uint64_t off; };      // off = output offset inside the stream
+  std::vector<ChainItem> chain;
+  std::vector<uint64_t>  off;                                      // per stream nchunk + 1 entries
+  std::vector<uint64_t>  end_bit(ns, 0);
+  uint64_t sym_total = 0, blk_total = 0;
+  uint32_t win_total = 0;
+  for (uint32_t i = 0; i < ns; i++) {
+    sd[i].off_base = (uint32_t)off.size();
+    sd[i].win_base = win_total;
+    sd[i].blk_base = blk_total;
+    sd[i].sym_base = sym_total;
+    sd[i].nchunk = 0; sd[i].nblk = 0; sd[i].total = 0;
+    if (!alive[i]) continue;
+    const SplitChunkOut* o = outs.data() + sd[i].cand_base;
+    const size_t chain0 = chain.size(), off0 = off.size();
+    uint64_t total = 0;
+    bool ok = true;
+    for (uint32_t k = 0;;) {
+      if ((o[k].status & 0xFF) == CH_FAIL) { ok = false; break; }
+      chain.push_back({i, k, total});
+      off.push_back(total);
+      total += o[k].out_bytes;
+      if (total > in[i].dstlen || total > 0xFFFFFFFFull) { ok = false; break; }
+      if (o[k].status == CH_FINAL) { end_bit[i] = o[k].end_bit; break; }
+      if (o[k].link <= k || o[k].link >= sd[i].ncand) { ok = false; break; }
+      k = o[k].link;
+    }
+    // markers index the 32 KiB before a chunk: they must exist
+    if (ok && chain.size() - chain0 > 1 && off[off0 + 1] < kWinBytes) ok = false;
+    if (!ok) { alive[i] = 0; chain.resize(chain0); off.resize(off0); continue; }
     off.push_back(total);
-    total += o.out_bytes;
-    if (total > dstlen || total > 0xFFFFFFFFull) return UNZ_NOOP;
-    if (o.status == CH_FINAL) { end_bit = o.end_bit; break; }
-    if (o.link <= i || o.link >= ncand) return UNZ_NOOP;
-    i = o.link;
+    sd[i].nchunk = (uint32_t)(chain.size() - chain0);
+    sd[i].total  = total;
+    sd[i].nblk   = (uint32_t)((total + kResolvePerBlock - 1) / kResolvePerBlock);
+    win_total += sd[i].nchunk - 1;
+    blk_total += sd[i].nblk;
+    sym_total += (total + 7) & ~7ull;
   }
-  off.push_back(total);
   const uint32_t nchunk = (uint32_t)chain.size();
-  if (nchunk > 1 && off[1] < kWinBytes) return UNZ_NOOP;   // markers index the 32 KiB before a chunk: they must exist
+  if (!nchunk) return UNZ_OK;
 
-  // ---- C: the chain decodes into 16-bit symbols at final offsets
-  // largest chunk first: the pass ends when its slowest warp does
+  // ---- C: the chains decode into 16-bit symbols at final offsets; largest chunk first (the pass ends when
+  // its slowest warp does)
   std::vector<uint32_t> perm(nchunk);
   std::iota(perm.begin(), perm.end(), 0u);
-  std::stable_sort(perm.begin(), perm.end(),
-                   [&](uint32_t a, uint32_t b) { return outs[chain[a]].out_bytes > outs[chain[b]].out_bytes; });
+  auto out_of = [&](uint32_t c) -> const SplitChunkOut& { return outs[sd[chain[c].stream].cand_base + chain[c].cand]; };
+  std::stable_sort(perm.begin(), perm.end(), [&](uint32_t a, uint32_t b) { return out_of(a).out_bytes > out_of(b).out_bytes; });
   for (uint32_t j = 0; j < nchunk; j++) {
-    const uint32_t k = perm[j];
-    jobs[j].cand = chain[k]; jobs[j].cap = outs[chain[k]].out_bytes; jobs[j].out_off = off[k];
-    jobs[j].tok_off = (uint64_t)tok_per_byte * (cand[chain[k]] >> 3);
+    const ChainItem& ci = chain[perm[j]];
+    const SplitStreamDesc& d = sd[ci.stream];
+    jobs[j].stream = ci.stream; jobs[j].pad = 0; jobs[j].cand = ci.cand;
+    jobs[j].cap = out_of(perm[j]).out_bytes; jobs[j].out_off = d.sym_base + ci.off;
+    jobs[j].tok_off = d.tok_base + (uint64_t)tok_per_byte * (cand[d.cand_base + ci.cand] >> 3);
     jobs[j].tok_cap = 0;
-    jobs[j].ntok = d_tok ? outs[chain[k]].ntok : kNoTokens;
+    jobs[j].ntok = d_tok ? out_of(perm[j]).ntok : kNoTokens;
   }
-  if (SB.d_sym.reserve((size_t)total * 2 + 64) || SB.d_off.reserve((size_t)(nchunk + 1) * 8)) return UNZ_ERR;
+  if (SB.d_sym.reserve((size_t)sym_total * 2 + 64) || SB.d_off.reserve(off.size() * 8) ||
+      SB.d_wbuf.reserve((size_t)win_total * kWinBytes + 64) || SB.d_partial.reserve((size_t)blk_total * 8 + 8) ||
+      upload_streams() != UNZ_OK)
+    return UNZ_ERR;
   CU_TRY(cudaMemcpyAsync(SB.d_jobs.p, jobs.data(), (size_t)nchunk * sizeof(SplitJob), cudaMemcpyHostToDevice, st), "H2D jobs");
-  CU_TRY(cudaMemcpyAsync(SB.d_off.p, off.data(), (size_t)(nchunk + 1) * 8, cudaMemcpyHostToDevice, st), "H2D offsets");
+  CU_TRY(cudaMemcpyAsync(SB.d_off.p, off.data(), off.size() * 8, cudaMemcpyHostToDevice, st), "H2D offsets");
   if (launch_chunks(false, nchunk, static_cast<uint16_t*>(SB.d_sym.p)) != UNZ_OK) return UNZ_ERR;
   mark("C decode pass");
-  if (trace) std::fprintf(stderr, "[split] ncand %u nchunk %u total %llu\n", ncand, nchunk, (unsigned long long)total);
+  if (trace) std::fprintf(stderr, "[split] streams %u ncand %u nchunk %u symbols %llu\n", ns, ncand, nchunk, (unsigned long long)sym_total);
   std::vector<SplitChunkOut> outs2(nchunk);
   CU_TRY(cudaMemcpyAsync(outs2.data(), SB.d_outs2.p, (size_t)nchunk * sizeof(SplitChunkOut), cudaMemcpyDeviceToHost, st), "D2H chunk results");
 
-  // ---- D: markers -> bytes, Adler-32
-  const uint32_t nblk = (uint32_t)((total + defl::kResolvePerBlock - 1) / defl::kResolvePerBlock);
-  std::vector<uint32_t> partial((size_t)nblk * 2);
-  if (nblk) {
-    if (SB.d_partial.reserve((size_t)nblk * 8)) return UNZ_ERR;
-    if (nchunk > 1) {
-      if (SB.d_wbuf.reserve((size_t)(nchunk - 1) * kWinBytes)) return UNZ_ERR;
-      window_resolve_kernel<<<(nchunk - 1) * 16u, 256, 0, st>>>(static_cast<uint16_t*>(SB.d_sym.p), static_cast<uint64_t*>(SB.d_off.p),
-                                                                nchunk, static_cast<uint8_t*>(SB.d_wbuf.p));
-      CU_TRY(cudaGetLastError(), "window_resolve_kernel launch");
-      g_launches.fetch_add(1, std::memory_order_relaxed);
-    }
-    marker_resolve_kernel<<<nblk, 256, 0, st>>>(static_cast<uint16_t*>(SB.d_sym.p), static_cast<uint64_t*>(SB.d_off.p), nchunk,
-                                                 static_cast<uint8_t*>(SB.d_wbuf.p), d_dst, total,
-                                                 static_cast<uint32_t*>(SB.d_partial.p));
+  // ---- D: windows, then markers -> bytes + Adler-32 partial sums
+  std::vector<uint32_t> partial((size_t)blk_total * 2);
+  if (win_total) {
+    window_resolve_kernel<<<win_total * 16u, 256, 0, st>>>(d_sd, ns, static_cast<uint16_t*>(SB.d_sym.p),
+                                                           static_cast<uint64_t*>(SB.d_off.p), static_cast<uint8_t*>(SB.d_wbuf.p));
+    CU_TRY(cudaGetLastError(), "window_resolve_kernel launch");
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+  }
+  if (blk_total) {
+    marker_resolve_kernel<<<(unsigned)blk_total, 256, 0, st>>>(d_sd, ns, static_cast<uint16_t*>(SB.d_sym.p),
+                                                                static_cast<uint64_t*>(SB.d_off.p), static_cast<uint8_t*>(SB.d_wbuf.p),
+                                                                static_cast<uint32_t*>(SB.d_partial.p));
     CU_TRY(cudaGetLastError(), "marker_resolve_kernel launch");
     g_launches.fetch_add(1, std::memory_order_relaxed);
-    CU_TRY(cudaMemcpyAsync(partial.data(), SB.d_partial.p, (size_t)nblk * 8, cudaMemcpyDeviceToHost, st), "D2H adler partials");
+    CU_TRY(cudaMemcpyAsync(partial.data(), SB.d_partial.p, (size_t)blk_total * 8, cudaMemcpyDeviceToHost, st), "D2H adler partials");
   }
-  uint8_t trailer[4] = {0, 0, 0, 0};
-  const uint64_t inpos = (end_bit + 7) >> 3;
-  const bool has_trailer = zlib && srclen - inpos >= 4;
-  if (has_trailer) CU_TRY(cudaMemcpyAsync(trailer, d_src + inpos, 4, cudaMemcpyDeviceToHost, st), "D2H trailer");
+  std::vector<uint8_t>  trailer((size_t)ns * 4, 0);
+  std::vector<uint64_t> inpos(ns, 0);
+  if (zlib) {
+    for (uint32_t i = 0; i < ns; i++) inpos[i] = (end_bit[i] + 7) >> 3;
+    CU_TRY(cudaMemcpyAsync(SB.d_at.p, inpos.data(), (size_t)ns * 8, cudaMemcpyHostToDevice, st), "H2D trailer offsets");
+    split_peek_kernel<<<(ns + 127) / 128, 128, 0, st>>>(d_sd, ns, static_cast<uint64_t*>(SB.d_at.p), 4u, static_cast<uint8_t*>(SB.d_peek.p));
+    CU_TRY(cudaGetLastError(), "split_peek_kernel launch");
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+    CU_TRY(cudaMemcpyAsync(trailer.data(), SB.d_peek.p, trailer.size(), cudaMemcpyDeviceToHost, st), "D2H trailers");
+  }
   CU_TRY(cudaStreamSynchronize(st), "split decode");
   mark("D marker resolve + adler");
+
+  // the decode pass must have reproduced the count pass (it cannot differ for a deterministic decode; the
+  // one-warp decoder has the last word if it ever does)
   for (uint32_t j = 0; j < nchunk; j++) {
-    const SplitChunkOut& a = outs[chain[perm[j]]];
+    const SplitChunkOut& a = out_of(perm[j]);
     const bool same = outs2[j].status == CH_REPLAYED
                           ? outs2[j].out_bytes == a.out_bytes
                           : (outs2[j].status == a.status && outs2[j].out_bytes == a.out_bytes && outs2[j].end_bit == a.end_bit);
-    if (!same)
-      return UNZ_NOOP;            // cannot happen for a deterministic decode; the one-warp decoder has the last word
+    if (!same) alive[chain[perm[j]].stream] = 0;
   }
-
-  uint64_t sa = 0, sw = 0;
-  for (uint32_t b = 0; b < nblk; b++) { sa += partial[2 * b]; sw += partial[2 * b + 1]; }
-  sa %= defl::kAdlerMod; sw %= defl::kAdlerMod;
-  const uint64_t nm = total % defl::kAdlerMod;
-  const uint32_t a = (uint32_t)((1 + sa) % defl::kAdlerMod);
-  const uint32_t b = (uint32_t)((nm + nm * sa + defl::kAdlerMod - sw) % defl::kAdlerMod);
-  std::memset(res, 0, sizeof(*res));
-  res->code = UNZ_OK;
-  res->adler = (b << 16) | a;
-  res->outlen = total;
-  res->inpos = inpos;
-  res->info = INFL_INFO_SPLIT_DECODE;
-  if (has_trailer) {
-    res->adler_stored = ((uint32_t)trailer[0] << 24) | ((uint32_t)trailer[1] << 16) | ((uint32_t)trailer[2] << 8) | trailer[3];
-    res->info |= INFL_INFO_HAS_TRAILER;
-    if (res->adler_stored == res->adler) res->info |= INFL_INFO_ADLER_MATCH;
+  for (uint32_t i = 0; i < ns; i++) {
+    if (!alive[i]) continue;
+    uint64_t sa = 0, sw = 0;
+    for (uint64_t b = sd[i].blk_base; b < sd[i].blk_base + sd[i].nblk; b++) { sa += partial[2 * b]; sw += partial[2 * b + 1]; }
+    sa %= defl::kAdlerMod; sw %= defl::kAdlerMod;
+    const uint64_t total = sd[i].total;
+    const uint64_t nm = total % defl::kAdlerMod;
+    const uint32_t a = (uint32_t)((1 + sa) % defl::kAdlerMod);
+    const uint32_t b = (uint32_t)((nm + nm * sa + defl::kAdlerMod - sw) % defl::kAdlerMod);
+    infl_batch_result_t* r = &res[i];
+    std::memset(r, 0, sizeof(*r));
+    r->code = UNZ_OK;
+    r->adler = (b << 16) | a;
+    r->outlen = total;
+    r->inpos = (end_bit[i] + 7) >> 3;
+    r->info = INFL_INFO_SPLIT_DECODE;
+    const bool has_trailer = zlib && in[i].srclen - r->inpos >= 4;
+    if (has_trailer) {
+      const uint8_t* t = &trailer[(size_t)i * 4];
+      r->adler_stored = ((uint32_t)t[0] << 24) | ((uint32_t)t[1] << 16) | ((uint32_t)t[2] << 8) | t[3];
+      r->info |= INFL_INFO_HAS_TRAILER;
+      if (r->adler_stored == r->adler) r->info |= INFL_INFO_ADLER_MATCH;
+    }
+    if (zlib && (flags & INFL_BATCH_VERIFY_ADLER) && (r->info & 3u) != 3u) {
+      r->code = UNZ_ERR;
+      r->info |= defl::R_ADLER << INFL_INFO_REASON_SHIFT;
+    }
+    status[i] = UNZ_OK;
+    g_split_decodes.fetch_add(1, std::memory_order_relaxed);
   }
-  if (zlib && (flags & INFL_BATCH_VERIFY_ADLER) && (res->info & 3u) != 3u) {
-    res->code = UNZ_ERR;
-    res->info |= defl::R_ADLER << INFL_INFO_REASON_SHIFT;
-  }
-  g_split_decodes.fetch_add(1, std::memory_order_relaxed);
   return UNZ_OK;
 }
 
+// one stream: UNZ_OK (decoded, *res filled) / UNZ_NOOP (take the one-warp decoder) / UNZ_ERR (engine failure)
+int split_decode_device(Engine* E, const uint8_t* d_src, uint64_t srclen, uint8_t* d_dst, uint64_t dstlen, int flags,
+                        void* d_ws, cudaStream_t st, infl_batch_result_t* res) {
+  SplitInput in{d_src, srclen, d_dst, dstlen};
+  int status = UNZ_NOOP;
+  if (split_decode_many(E, &in, 1, flags, d_ws, st, res, &status) != UNZ_OK) return UNZ_ERR;
+  return status;
+}
+
+// Which streams of a batch go through the split decoder: the very large ones always; in a batch, those whose
+// one-warp decode would outlast the rest of the batch (bytes x resident warps > half the batch's bytes).
+static const uint64_t kSplitMinInBatch = 256ull << 10;    // compressed bytes below which splitting never pays
+bool wants_split(const infl_batch_item_t& it, uint64_t batch_bytes, uint64_t resident_warps) {
+  if (it.srclen > 0xFFFFFFFFull || it.dstlen > 0xFFFFFFFFull) return false;
+  if (it.srclen >= kSplitMinBytes) return true;
+  if (it.srclen < kSplitMinInBatch) return false;
+  // DEFL_SPLIT_TAIL_PCT: a stream is split when its share of the batch exceeds this percentage of 1 / resident warps
+  static const uint32_t pct = env_u32("DEFL_SPLIT_TAIL_PCT", 25u, 1u, 100000u);
+  return (it.srclen + it.dstlen) * resident_warps * 100u > batch_bytes * pct;
+}
+
 // ---- host-pointer batch on ONE device: stage in, decode, stage out ----------------------------------------
-// The batch is cut into chunks that run through a two-slot pipeline: while chunk c decodes, chunk c+1's
+// The batch is cut into chunks that run through a three-slot pipeline: while chunk c decodes, chunk c+1's
 // input is on its way to the device and chunk c-1's output on its way back (separate copy engines).
 // Inputs that are (nearly) adjacent in host memory travel as one copy; adjacent outputs do too.
 struct HostRun { const uint8_t* h; size_t len; size_t dev_off; size_t first; size_t count; };
@@ -500,15 +621,16 @@ struct PipeSlot {
   size_t first = 0, count = 0;
 };
 
+constexpr int kPipeSlots = 3;    // chunk c+1 is on its way in while chunk c decodes and chunk c-1 is on its way out
 struct HostPipe {
-  PipeSlot slot[2];
+  PipeSlot slot[kPipeSlots];
   bool     ready = false;
 };
 HostPipe g_pipes[kMaxDevices];
 
 constexpr size_t kGapMerge   = 512;          // input runs this close in host memory are copied as one
 constexpr size_t kChunkMin   = 96u << 20;    // bytes (in + out) per chunk, at least
-constexpr size_t kChunkCount = 8;            // aim for this many chunks in a large batch
+constexpr size_t kChunkCount = 12;           // aim for this many chunks in a large batch
 
 int chunk_submit(Engine* E, PipeSlot& S, const infl_batch_item_t* items, size_t first, size_t count, int flags) {
   cudaStream_t st = S.st;
@@ -665,14 +787,14 @@ int run_host_batch_on_device(const infl_batch_item_t* items, size_t n, int flags
       bytes += items[first + count].srclen + items[first + count].dstlen;
       count++;
     }
-    PipeSlot& S = HP.slot[c & 1];
-    if (c >= 2) rc = (cudaStreamSynchronize(S.st) == cudaSuccess) ? UNZ_OK : fail("D2H output");   // chunk c-2 is home
+    PipeSlot& S = HP.slot[c % kPipeSlots];
+    if (c >= kPipeSlots) rc = (cudaStreamSynchronize(S.st) == cudaSuccess) ? UNZ_OK : fail("D2H output");   // its last chunk is home
     if (rc == UNZ_OK) rc = chunk_submit(E, S, items, first, count, flags);
-    if (rc == UNZ_OK && c >= 1) rc = chunk_finish(HP.slot[(c - 1) & 1], items, results);
+    if (rc == UNZ_OK && c >= 1) rc = chunk_finish(HP.slot[(c - 1) % kPipeSlots], items, results);
     first += count;
     c++;
   }
-  if (rc == UNZ_OK && c >= 1) rc = chunk_finish(HP.slot[(c - 1) & 1], items, results);
+  if (rc == UNZ_OK && c >= 1) rc = chunk_finish(HP.slot[(c - 1) % kPipeSlots], items, results);
   for (PipeSlot& S : HP.slot) {
     const cudaError_t e = cudaStreamSynchronize(S.st);
     if (e != cudaSuccess && rc == UNZ_OK) rc = fail("D2H output", e);
@@ -690,21 +812,35 @@ int run_device_batch(const infl_batch_item_t* items, size_t n, int flags, infl_b
       E->d_order.reserve(n * sizeof(uint32_t)) || E->d_ws.reserve_exact(warp_kernel_workspace(E->sms)) ||
       E->h_order.reserve(n * sizeof(uint32_t)))
     return UNZ_ERR;
-  // large streams go through the split-point decoder, one after another; the rest is one batch launch
+  // streams that would outlast the rest of the batch on one warp go through the split decoder, all of them
+  // together; the rest is one batch launch
   std::vector<infl_batch_item_t> rest;
   std::vector<size_t>            rest_idx;
   bool any_split = false;
+  uint64_t batch_bytes = 0;
+  int grid_ctas = 0;
+  if (warp_kernel_grid(E->sms, &grid_ctas) != UNZ_OK) return UNZ_ERR;
+  const uint64_t resident = (uint64_t)grid_ctas * kWarpsPerCta;
+  for (size_t i = 0; i < n; i++) batch_bytes += items[i].srclen + items[i].dstlen;
   if (!(flags & INFL_BATCH_NO_SPLIT))
-    for (size_t i = 0; i < n; i++)
-      if (items[i].srclen >= kSplitMinBytes && items[i].srclen <= 0xFFFFFFFFull && items[i].dstlen <= 0xFFFFFFFFull) any_split = true;
+    for (size_t i = 0; i < n && !any_split; i++) any_split = wants_split(items[i], batch_bytes, resident);
   if (any_split) {
+    std::vector<SplitInput> sin;
+    std::vector<size_t>     sin_idx;
     for (size_t i = 0; i < n; i++) {
-      int rc = UNZ_NOOP;
-      if (items[i].srclen >= kSplitMinBytes && items[i].srclen <= 0xFFFFFFFFull && items[i].dstlen <= 0xFFFFFFFFull)
-        rc = split_decode_device(E, static_cast<const uint8_t*>(items[i].src), items[i].srclen,
-                                 static_cast<uint8_t*>(items[i].dst), items[i].dstlen, flags, E->d_ws.p, st, &results[i]);
-      if (rc == UNZ_ERR) return UNZ_ERR;
-      if (rc == UNZ_NOOP) { rest.push_back(items[i]); rest_idx.push_back(i); }
+      if (wants_split(items[i], batch_bytes, resident)) {
+        sin.push_back({static_cast<const uint8_t*>(items[i].src), items[i].srclen, static_cast<uint8_t*>(items[i].dst), items[i].dstlen});
+        sin_idx.push_back(i);
+      } else {
+        rest.push_back(items[i]); rest_idx.push_back(i);
+      }
+    }
+    std::vector<infl_batch_result_t> sres(sin.size());
+    std::vector<int>                 sstat(sin.size(), UNZ_NOOP);
+    if (split_decode_many(E, sin.data(), sin.size(), flags, E->d_ws.p, st, sres.data(), sstat.data()) != UNZ_OK) return UNZ_ERR;
+    for (size_t k = 0; k < sin.size(); k++) {
+      if (sstat[k] == UNZ_OK) results[sin_idx[k]] = sres[k];
+      else { rest.push_back(items[sin_idx[k]]); rest_idx.push_back(sin_idx[k]); }
     }
     if (rest.empty()) return UNZ_OK;
     std::vector<infl_batch_result_t> rr(rest.size());

@@ -34,8 +34,37 @@ struct SplitChunkOut {
   uint32_t ntok;        // COUNT: tokens kept for the DECODE pass, or kNoTokens
 };
 
+// One stream of a split decode.  All the kernels below work on MANY streams at once: a table of these plus
+// cumulative bases (granules, candidates, chunks, windows, D2 blocks) says which stream a unit belongs to.
+struct SplitStreamDesc {
+  const uint8_t* src;
+  uint8_t*       dst;
+  uint64_t srclen;
+  uint64_t total;        // output bytes (known after the count pass)
+  uint64_t sym_base;     // first 16-bit symbol of the stream in sym[] (a multiple of 8)
+  uint64_t tok_base;     // first kept token of the stream in tokbuf[]
+  uint64_t blk_base;     // first D2 block of the stream (also its slot in partial[])
+  uint32_t body;         // bytes of zlib header in front of the deflate data
+  uint32_t gran_base, ngran;   // F: granules searched
+  uint32_t cand_base, ncand;   // candidates in cand[], stream-relative bit positions, increasing
+  uint32_t off_base, nchunk;   // chain chunks: off[off_base .. off_base + nchunk] = output offsets
+  uint32_t win_base;           // first of the stream's nchunk - 1 resolved windows in wbuf
+  uint32_t nblk;               // D2 blocks
+  uint32_t pad;
+};
+
+// the stream that owns unit x: the last one whose base is <= x (streams without units share their successor's base)
+template <typename F>
+DEFL_DEV uint32_t stream_of(uint32_t nstreams, uint64_t x, F base_of) {
+  uint32_t lo = 0, hi = nstreams;
+  while (hi - lo > 1u) { const uint32_t mid = (lo + hi) >> 1; if (base_of(mid) <= x) lo = mid; else hi = mid; }
+  return lo;
+}
+
 struct SplitJob {
-  uint32_t cand;        // index into cand[]: where the chunk starts
+  uint32_t stream;      // index into the stream table
+  uint32_t pad;
+  uint32_t cand;        // index into the stream's candidates: where the chunk starts
   uint32_t cap;         // DECODE: exactly the bytes the COUNT pass reported
   uint64_t out_off;     // DECODE: offset of the chunk's first symbol
   uint64_t tok_off;     // where the chunk's tokens are kept (COUNT writes, DECODE reads)
@@ -138,8 +167,8 @@ DEFL_DEV void inflate_chunk_warp(WarpSmem& sm, const WarpScratch& sc, int lane, 
 #ifdef __CUDACC__
 template <bool COUNT, int WARPS>
 __global__ void __launch_bounds__(WARPS * 32, 32 / WARPS)
-split_chunk_kernel(const uint8_t* __restrict__ src, uint32_t srclen, const uint64_t* __restrict__ cand,
-                   uint32_t ncand, const SplitJob* __restrict__ jobs, uint32_t njobs, uint16_t* __restrict__ sym,
+split_chunk_kernel(const SplitStreamDesc* __restrict__ streams, const uint64_t* __restrict__ cand,
+                   const SplitJob* __restrict__ jobs, uint32_t njobs, uint16_t* __restrict__ sym,
                    SplitChunkOut* __restrict__ outs, unsigned int* __restrict__ ticket,
                    unsigned char* __restrict__ scratch, uint32_t* __restrict__ tokbuf) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -152,18 +181,29 @@ split_chunk_kernel(const uint8_t* __restrict__ src, uint32_t srclen, const uint6
     k = simt::shfl(kFull, k, 0);
     if (k >= njobs) break;
     const SplitJob job = jobs[k];
+    const SplitStreamDesc& sd = streams[job.stream];
     SplitChunkOut  o;
     TokSink        sink;
     sink.buf = (COUNT && tokbuf) ? tokbuf + job.tok_off : nullptr;
     sink.cap = job.tok_cap; sink.n = 0; sink.ok = sink.buf != nullptr;
     // the chunk that starts the stream has no unknown window before it
-    inflate_chunk_warp<uint16_t, COUNT>(sm, sc, lane, src, srclen, cand, ncand, job.cand,
+    inflate_chunk_warp<uint16_t, COUNT>(sm, sc, lane, sd.src, (uint32_t)sd.srclen, cand + sd.cand_base, sd.ncand, job.cand,
                                         COUNT ? nullptr : sym + job.out_off, COUNT ? 0xFFFFFFFFu : job.cap,
                                         job.cand == 0u ? 0u : 32768u, o, COUNT ? &sink : nullptr,
                                         (!COUNT && tokbuf) ? tokbuf + job.tok_off : nullptr, job.ntok);
     if (lane == 0) outs[k] = o;
     simt::syncwarp(kFull);
   }
+}
+
+// first two bytes of every stream (zlib header check on the host) / the four bytes at a given offset (Adler trailer)
+__global__ void split_peek_kernel(const SplitStreamDesc* __restrict__ streams, uint32_t nstreams,
+                                  const uint64_t* __restrict__ at, uint32_t nbytes, uint8_t* __restrict__ out) {
+  const uint32_t s = blockIdx.x * blockDim.x + threadIdx.x;
+  if (s >= nstreams) return;
+  const uint64_t a = at ? at[s] : 0u;
+  for (uint32_t i = 0; i < nbytes; i++)
+    out[s * nbytes + i] = a + i < streams[s].srclen ? streams[s].src[a + i] : (uint8_t)0;
 }
 
 #endif  // __CUDACC__
@@ -312,7 +352,7 @@ struct FindSmem {
 
 template <int WARPS>
 __global__ void __launch_bounds__(WARPS * 32)
-find_block_starts_kernel(const uint8_t* __restrict__ src, uint32_t srclen, uint32_t body, uint32_t ngran,
+find_block_starts_kernel(const SplitStreamDesc* __restrict__ streams, uint32_t nstreams, uint32_t ngran_total,
                          uint32_t granule_bytes, uint64_t* __restrict__ found) {
   __shared__ FindSmem fsm[WARPS];
   __shared__ uint8_t  kraft9[512];
@@ -323,8 +363,12 @@ find_block_starts_kernel(const uint8_t* __restrict__ src, uint32_t srclen, uint3
   __syncthreads();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   FindSmem& fs = fsm[warp];
-  const uint32_t g = blockIdx.x * WARPS + warp;
-  if (g >= ngran) return;
+  const uint32_t gg = blockIdx.x * WARPS + warp;          // granule number over all streams
+  if (gg >= ngran_total) return;
+  const SplitStreamDesc& sd = streams[stream_of(nstreams, gg, [&](uint32_t i) { return (uint64_t)streams[i].gran_base; })];
+  const uint8_t* const src = sd.src;
+  const uint32_t srclen = (uint32_t)sd.srclen, body = sd.body;
+  const uint32_t g = gg - sd.gran_base;
   const unsigned lt = simt::lanemask_lt();
   const uint32_t mis      = (uint32_t)((uintptr_t)src & 3u);
   const uint64_t base_bit = (uint64_t)mis * 8u;
@@ -410,7 +454,7 @@ find_block_starts_kernel(const uint8_t* __restrict__ src, uint32_t srclen, uint3
   }
 #pragma unroll 1
   while (result == kNoCandidate && npend > 0u) parse_round();
-  if (lane == 0) found[g] = result;
+  if (lane == 0) found[gg] = result;
 }
 
 #endif  // __CUDACC__
@@ -442,9 +486,15 @@ constexpr uint32_t kWinBytes        = 32768;
 constexpr uint32_t kResolvePerBlock = 65536;      // output bytes per D2 block
 
 __global__ void __launch_bounds__(256)
-window_resolve_kernel(const uint16_t* __restrict__ sym, const uint64_t* __restrict__ off, uint32_t nchunk,
-                      uint8_t* __restrict__ wbuf) {
-  const uint32_t c  = 1u + blockIdx.x / 16u;                      // 16 blocks x 2048 symbols per window
+window_resolve_kernel(const SplitStreamDesc* __restrict__ streams, uint32_t nstreams, const uint16_t* __restrict__ sym_all,
+                      const uint64_t* __restrict__ off_all, uint8_t* __restrict__ wbuf_all) {
+  const uint32_t wi = blockIdx.x / 16u;                           // window number over all streams; 16 blocks x 2048 symbols each
+  const SplitStreamDesc& sd = streams[stream_of(nstreams, wi, [&](uint32_t i) { return (uint64_t)streams[i].win_base; })];
+  const uint16_t* const sym  = sym_all + sd.sym_base;
+  const uint64_t* const off  = off_all + sd.off_base;
+  uint8_t* const        wbuf = wbuf_all + (size_t)sd.win_base * kWinBytes;
+  const uint32_t nchunk = sd.nchunk;
+  const uint32_t c  = 1u + (wi - sd.win_base);
   const uint32_t k0 = (blockIdx.x % 16u) * 2048u + threadIdx.x * 8u;
   if (c >= nchunk) return;
   const uint64_t base = off[c] - kWinBytes;                       // the host made sure off[c] >= 32 KiB
@@ -467,12 +517,19 @@ window_resolve_kernel(const uint16_t* __restrict__ sym, const uint64_t* __restri
 }
 
 __global__ void __launch_bounds__(256)
-marker_resolve_kernel(const uint16_t* __restrict__ sym, const uint64_t* __restrict__ off, uint32_t nchunk,
-                      const uint8_t* __restrict__ wbuf, uint8_t* __restrict__ dst, uint64_t total,
+marker_resolve_kernel(const SplitStreamDesc* __restrict__ streams, uint32_t nstreams, const uint16_t* __restrict__ sym_all,
+                      const uint64_t* __restrict__ off_all, const uint8_t* __restrict__ wbuf_all,
                       uint32_t* __restrict__ partial) {
   __shared__ __align__(16) uint8_t win[kWinBytes];
   __shared__ uint32_t sa[8], sw[8], sc0;
-  const uint64_t b0 = (uint64_t)blockIdx.x * kResolvePerBlock;
+  const SplitStreamDesc& sd = streams[stream_of(nstreams, blockIdx.x, [&](uint32_t i) { return streams[i].blk_base; })];
+  const uint16_t* const sym  = sym_all + sd.sym_base;
+  const uint64_t* const off  = off_all + sd.off_base;
+  const uint8_t* const  wbuf = wbuf_all + (size_t)sd.win_base * kWinBytes;
+  uint8_t* const        dst  = sd.dst;
+  const uint32_t nchunk = sd.nchunk;
+  const uint64_t total  = sd.total;
+  const uint64_t b0 = (uint64_t)(blockIdx.x - sd.blk_base) * kResolvePerBlock;
   const uint64_t b1 = b0 + kResolvePerBlock < total ? b0 + kResolvePerBlock : total;
   if (threadIdx.x == 0) {          // the chunk that holds this block's first position
     uint32_t lo = 0, hi = nchunk;

@@ -361,3 +361,48 @@ def test_split_single_large_stream(gpu_lib):
         assert int(g["code"]) == code
         if code == 0:
             assert bytes(out) == want and int(g["adler"]) == r.adler
+
+
+@pytest.mark.gpu
+def test_split_many_streams_in_one_batch(gpu_lib):
+    """BASELINE.json configs[4] in small: a device-resident batch whose large members would outlast the rest on
+    one warp each.  They go through the split decoder TOGETHER (one launch sequence for all of them), the small
+    ones and the unsplittable ones (stored, fixed Huffman) through the warp-per-stream kernel; every record
+    equals the oracle's."""
+    import torch
+    from defl_b200 import synth, api
+    d = gpu_lib
+    Z = zlib.Z_DEFAULT_STRATEGY
+    specs = [("text", 3 << 20, 1, 6, Z), ("log", 4 << 20, 2, 9, Z), ("png", 2 << 20, 3, 1, Z), ("text", 1500000, 4, 1, Z),
+             ("rand", 1 << 20, 5, 6, Z), ("text", 2 << 20, 6, 6, zlib.Z_FIXED), ("zero", 3 << 20, 7, 6, Z),
+             ("text", 700000, 8, 9, Z), ("log", 70000, 9, 6, Z), ("text", 65536, 10, 6, Z), ("png", 900000, 11, 6, Z),
+             ("text", 4000000, 12, 6, Z)]
+    streams = synth.make_streams(specs, threads=4)
+    dev = torch.device("cuda", 0)
+    srcs = [torch.frombuffer(bytearray(z), dtype=torch.uint8).to(dev) for _, z in streams]
+    dsts = [torch.zeros(len(r) + 8, dtype=torch.uint8, device=dev) for r, _ in streams]
+    items = np.zeros(len(streams), dtype=d.ITEM_DTYPE)
+    for i, ((raw, z), s, t) in enumerate(zip(streams, srcs, dsts)):
+        items[i] = (s.data_ptr(), len(z), t.data_ptr() + (i % 3), len(raw))      # outputs at odd alignments too
+    results = np.zeros(len(streams), dtype=d.RESULT_DTYPE)
+    flags = d.INFL_ZLIB | d.INFL_BATCH_VERIFY_ADLER | d.INFL_BATCH_DEVICE_PTRS
+    api.infl_buf_batch_raw(items, flags, results)
+    torch.cuda.synchronize()
+    nsplit = 0
+    for i, ((raw, z), t, g) in enumerate(zip(streams, dsts, results)):
+        code, want, r = ol.port_inflate(z, len(raw), 1)
+        assert code == 0 and int(g["code"]) == 0, (i, int(g["code"]), int(g["info"]))
+        assert int(g["outlen"]) == len(raw) and int(g["inpos"]) == r.inpos
+        assert int(g["adler"]) == r.adler == int(g["adler_stored"])
+        assert t[(i % 3): (i % 3) + len(raw)].cpu().numpy().tobytes() == raw, i
+        nsplit += bool(int(g["info"]) & 4)
+    assert nsplit >= 6, nsplit
+    # a damaged member: same verdict as the oracle, the others unharmed
+    bad = bytearray(streams[0][1]); bad[len(bad) // 2] ^= 0x40
+    tb = torch.frombuffer(bad, dtype=torch.uint8).to(dev)
+    items[0]["src"] = tb.data_ptr()
+    api.infl_buf_batch_raw(items, flags, results)
+    code, _, _ = ol.port_inflate(bytes(bad), len(streams[0][0]), 1)
+    exp = code if code != 0 else (0 if zlib.adler32(ol.port_inflate(bytes(bad), len(streams[0][0]), 1)[1]) else 0)
+    assert (int(results[0]["code"]) == 0) == (code == 0 and int(results[0]["adler"]) == int(results[0]["adler_stored"]))
+    assert all(int(g["code"]) == 0 for g in results[1:])
