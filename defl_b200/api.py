@@ -37,6 +37,7 @@ EXPORTED_SYMBOLS = [
     "infl_destroy", "infl_buf", "infl_stream", "infl_output_pos", "infl_input_pos", "infl_adler32",
     "infl_buf_batch", "infl_buf_batch_iov", "infl_batch_workspace_size", "infl_batch_decode_device",
     "infl_gather_device",
+    "infl_batch_partition",
     "infl_device_count", "infl_last_error", "infl_engine_info",
     "infl_kernel_launch_count", "infl_set_lanes_per_stream", "infl_set_pipeline_shape", "infl_set_engine",
 ]
@@ -87,6 +88,8 @@ def lib():
     L.infl_batch_workspace_size.argtypes = [sz]
     L.infl_batch_decode_device.restype = i32
     L.infl_batch_decode_device.argtypes = [vp, vp, sz, i32, vp, vp, vp]
+    L.infl_batch_partition.restype = i32
+    L.infl_batch_partition.argtypes = [vp, sz, i32, vp, vp]
     L.infl_gather_device.restype = i32
     L.infl_gather_device.argtypes = [vp, vp, vp, sz, vp, vp]
     L.infl_device_count.restype = i32
@@ -228,6 +231,20 @@ def infl_buf_batch(srcs, dstlens, flags=0):
     if rc != UNZ_OK:
         raise RuntimeError("infl_buf_batch: " + last_error())
     return res, [o[: int(r["outlen"])] for o, r in zip(outs, res)]
+
+
+def batch_partition(srclens, dstlens, nparts):
+    """Byte-balanced shards of independent streams (no device needed): -> (part_of[n], shard_bytes[nparts])."""
+    n = len(srclens)
+    items = np.zeros(n, dtype=ITEM_DTYPE)
+    items["srclen"] = np.asarray(srclens, dtype=np.uint64)
+    items["dstlen"] = np.asarray(dstlens, dtype=np.uint64)
+    part = np.zeros(n, dtype=np.uint32)
+    load = np.zeros(nparts, dtype=np.uint64)
+    rc = lib().infl_batch_partition(items.ctypes.data, n, int(nparts), part.ctypes.data, load.ctypes.data)
+    if rc != UNZ_OK:
+        raise RuntimeError("infl_batch_partition: " + last_error())
+    return part, load
 
 
 def infl_buf_batch_raw(items, flags, results):
