@@ -170,8 +170,7 @@ def run_reference_arm(args, rank, world):
     src_off = np.zeros(n + 1, dtype=np.uint64)
     src_off[:n] = so
     src_off[n] = so[-1] + sl[-1]
-    if raw_lens is None:
-        raw_lens = [STREAM_BYTES] * n
+    raw_lens = [STREAM_BYTES] * n
     dst_off = np.concatenate([[0], np.cumsum(np.asarray(raw_lens, dtype=np.uint64))]).astype(np.uint64)
     out_total = int(dst_off[-1])
     dst = np.zeros(out_total, dtype=np.uint8)
