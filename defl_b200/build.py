@@ -39,7 +39,8 @@ def stale():
 def build(force=False, verbose=False):
     if not force and not stale():
         return LIB
-    cmd = [_nvcc()] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + \
+    extra = os.environ.get("DEFL_NVCC_EXTRA", "").split()          # experiments only (e.g. -DDEFL_WARP_CTAS_PER_SM=10)
+    cmd = [_nvcc()] + NVCC_FLAGS + extra + (["-Xptxas", "-v"] if verbose else []) + \
           ["-o", LIB] + [os.path.join(CSRC, s) for s in SOURCES]
     out = subprocess.run(cmd, capture_output=True, text=True)
     if out.returncode != 0:

@@ -92,7 +92,10 @@ constexpr size_t pipeline_smem_bytes() { return sizeof(Slot) * D * SL + sizeof(W
 // once (warp_decode.cuh).  Persistent CTAs of WARPS warps; each warp owns a slice of the global token
 // scratch and pulls streams from the ticket counter.
 template <int WARPS>
-__global__ void __launch_bounds__(WARPS * 32, 32 / WARPS)
+#ifndef DEFL_WARP_CTAS_PER_SM
+#define DEFL_WARP_CTAS_PER_SM 8      // x 4 warps: 32 resident warps per SM at 64 registers (10 -> 48 registers spills, 6 gains nothing)
+#endif
+__global__ void __launch_bounds__(WARPS * 32, DEFL_WARP_CTAS_PER_SM)
 inflate_warp_kernel(const infl_batch_item_t* __restrict__ items, const uint32_t* __restrict__ order,
                     uint32_t n, int flags, infl_batch_result_t* __restrict__ results,
                     unsigned int* __restrict__ ticket, unsigned char* __restrict__ scratch) {
