@@ -316,6 +316,8 @@ int split_decode_many(Engine* E, const SplitInput* in, size_t nin, int flags, vo
   static const uint32_t granule = env_u32("DEFL_SPLIT_GRANULE", 32768u, 4096u, 1u << 24);
   static const uint64_t min_gap = (uint64_t)env_u32("DEFL_SPLIT_GAP", 40960u, 0u, 1u << 28) * 8u;   // bits
   static const uint32_t tok_per_byte = env_u32("DEFL_SPLIT_TOKENS_PER_BYTE", 2u, 0u, 32u);
+  static const bool     fixed_mid = env_u32("DEFL_SPLIT_FIXED", 1u, 0u, 1u) != 0u;
+  static const uint32_t probe_bits = env_u32("DEFL_SPLIT_PROBE_BITS", 8192u, 256u, 1u << 20);
 
   int grid_warps = 0;
   if (warp_kernel_grid(E->sms, &grid_warps) != UNZ_OK) return UNZ_ERR;      // CTAs of kWarpsPerCta warps
@@ -330,7 +332,7 @@ int split_decode_many(Engine* E, const SplitInput* in, size_t nin, int flags, vo
     sd[i].src = in[i].d_src; sd[i].dst = in[i].d_dst; sd[i].srclen = in[i].srclen;
     if (in[i].srclen > 0xFFFFFFFFull || in[i].dstlen > 0xFFFFFFFFull || in[i].srclen < 64) alive[i] = 0;
   }
-  if (SB.d_streams.reserve((size_t)ns * sizeof(SplitStreamDesc)) || SB.d_peek.reserve((size_t)ns * 4) || SB.d_at.reserve((size_t)ns * 8))
+  if (SB.d_streams.reserve((size_t)ns * sizeof(SplitStreamDesc)) || SB.d_peek.reserve((size_t)ns * 4 + 16) || SB.d_at.reserve((size_t)ns * 8))
     return UNZ_ERR;
   auto* d_sd = static_cast<SplitStreamDesc*>(SB.d_streams.p);
   auto upload_streams = [&]() -> int {
@@ -338,19 +340,28 @@ int split_decode_many(Engine* E, const SplitInput* in, size_t nin, int flags, vo
     return UNZ_OK;
   };
 
-  // ---- zlib headers
-  if (zlib) {
+  // ---- zlib headers, and the type of each stream's first block
+  {
     if (upload_streams() != UNZ_OK) return UNZ_ERR;
-    std::vector<uint8_t> h2((size_t)ns * 2);
-    split_peek_kernel<<<(ns + 127) / 128, 128, 0, st>>>(d_sd, ns, nullptr, 2u, static_cast<uint8_t*>(SB.d_peek.p));
+    std::vector<uint8_t> h3((size_t)ns * 3);
+    split_peek_kernel<<<(ns + 127) / 128, 128, 0, st>>>(d_sd, ns, nullptr, 3u, static_cast<uint8_t*>(SB.d_peek.p));
     CU_TRY(cudaGetLastError(), "split_peek_kernel launch");
     g_launches.fetch_add(1, std::memory_order_relaxed);
-    CU_TRY(cudaMemcpyAsync(h2.data(), SB.d_peek.p, h2.size(), cudaMemcpyDeviceToHost, st), "D2H zlib headers");
-    CU_TRY(cudaStreamSynchronize(st), "D2H zlib headers");
+    CU_TRY(cudaMemcpyAsync(h3.data(), SB.d_peek.p, h3.size(), cudaMemcpyDeviceToHost, st), "D2H stream heads");
+    CU_TRY(cudaStreamSynchronize(st), "D2H stream heads");
     for (uint32_t i = 0; i < ns; i++) {
-      const uint8_t c0 = h2[2 * i], c1 = h2[2 * i + 1];
-      if ((c0 & 15) != 8 || (c0 >> 4) > 7 || ((c0 << 8) + c1) % 31 != 0 || (c1 & 0x20)) alive[i] = 0;
-      sd[i].body = 2;
+      const uint8_t c0 = h3[3 * i], c1 = h3[3 * i + 1];
+      if (zlib) {
+        if ((c0 & 15) != 8 || (c0 >> 4) > 7 || ((c0 << 8) + c1) % 31 != 0 || (c1 & 0x20)) alive[i] = 0;
+        sd[i].body = 2;
+      }
+      const uint32_t btype = (h3[3 * i + (zlib ? 2 : 0)] >> 1) & 3u;
+      // a stream that opens with a fixed-Huffman block has no block headers worth searching for (Z_FIXED output is
+      // fixed blocks throughout): its chunks start on token boundaries inside the blocks instead
+      sd[i].mode = (btype == 1u && fixed_mid) ? MODE_FIXED_MID : MODE_BLOCK_STARTS;
+      // a stream that opens with a stored block is almost always stored throughout (incompressible data): nothing
+      // to find, and one warp copies it at memory speed anyway
+      if (btype == 0u || btype == 3u) alive[i] = 0;
     }
   }
 
@@ -367,6 +378,15 @@ int split_decode_many(Engine* E, const SplitInput* in, size_t nin, int flags, vo
       d_sd, ns, ngran_total, granule, static_cast<uint64_t*>(SB.d_found.p));
   CU_TRY(cudaGetLastError(), "find_block_starts_kernel launch");
   g_launches.fetch_add(1, std::memory_order_relaxed);
+  bool any_fixed = false;
+  for (uint32_t i = 0; i < ns; i++) any_fixed = any_fixed || (alive[i] && sd[i].mode == MODE_FIXED_MID);
+  if (any_fixed) {
+    const unsigned per_cta = kWarpsPerCta * 32;
+    fixed_probe_kernel<kWarpsPerCta><<<(ngran_total + per_cta - 1) / per_cta, per_cta, sizeof(WarpSmem) * kWarpsPerCta, st>>>(
+        d_sd, ns, ngran_total, granule, probe_bits, static_cast<uint64_t*>(SB.d_found.p));
+    CU_TRY(cudaGetLastError(), "fixed_probe_kernel launch");
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+  }
   std::vector<uint64_t> found(ngran_total);
   CU_TRY(cudaMemcpyAsync(found.data(), SB.d_found.p, (size_t)ngran_total * 8, cudaMemcpyDeviceToHost, st), "D2H block starts");
   CU_TRY(cudaStreamSynchronize(st), "find_block_starts_kernel");
@@ -381,7 +401,7 @@ int split_decode_many(Engine* E, const SplitInput* in, size_t nin, int flags, vo
       if (f != kNoCandidate && f >= cand.back() + min_gap && f > cand.back()) cand.push_back(f);
     }
     sd[i].ncand = (uint32_t)cand.size() - sd[i].cand_base;
-    if (sd[i].ncand < 8) { alive[i] = 0; cand.resize(sd[i].cand_base); sd[i].ncand = 0; }
+    if (sd[i].ncand < 4) { alive[i] = 0; cand.resize(sd[i].cand_base); sd[i].ncand = 0; }
   }
   const uint32_t ncand = (uint32_t)cand.size();
   if (!ncand) return UNZ_OK;
@@ -406,7 +426,7 @@ int split_decode_many(Engine* E, const SplitInput* in, size_t nin, int flags, vo
       for (uint32_t k = 0; k < sd[i].ncand; k++, j++) {
         const uint64_t* c = cand.data() + sd[i].cand_base;
         const uint64_t b0 = c[k] >> 3, b1 = k + 1 < sd[i].ncand ? c[k + 1] >> 3 : in[i].srclen;
-        jobs[j].stream = i; jobs[j].pad = 0; jobs[j].cand = k; jobs[j].cap = 0; jobs[j].out_off = 0;
+        jobs[j].stream = i; jobs[j].start_final = FIN_UNKNOWN; jobs[j].cand = k; jobs[j].cap = 0; jobs[j].out_off = 0;
         jobs[j].tok_off = sd[i].tok_base + (uint64_t)tok_per_byte * b0;
         jobs[j].tok_cap = (uint32_t)std::min<uint64_t>((uint64_t)tok_per_byte * (b1 - b0), 0xFFFFFFF0ull);
         jobs[j].ntok = kNoTokens;
@@ -446,7 +466,9 @@ int split_decode_many(Engine* E, const SplitInput* in, size_t nin, int flags, vo
   mark("A count pass");
 
   // ---- per stream, the chain of true chunks from its first block to its final block
-  struct ChainItem { uint32_t stream, cand; uint64_t off; };      // off = output offset inside the stream
+  // A chunk that starts inside a block (MODE_FIXED_MID) learns from its predecessor whether that block is the
+  // stream's last one; if it is, the chunk ends at that block's end-of-block code (eob_* of its record).
+  struct ChainItem { uint32_t stream, cand; uint64_t off; uint32_t bytes, ntok, start_final; bool ends; };   // off = offset inside the stream
   std::vector<ChainItem> chain;
   std::vector<uint64_t>  off;                                      // per stream nchunk + 1 entries
   std::vector<uint64_t>  end_bit(ns, 0);
@@ -463,14 +485,20 @@ int split_decode_many(Engine* E, const SplitInput* in, size_t nin, int flags, vo
     const size_t chain0 = chain.size(), off0 = off.size();
     uint64_t total = 0;
     bool ok = true;
+    uint32_t fin = FIN_NO;                 // finality of the block chunk k starts in (meaningful for mid-block starts)
     for (uint32_t k = 0;;) {
-      if ((o[k].status & 0xFF) == CH_FAIL) { ok = false; break; }
-      chain.push_back({i, k, total});
+      if ((o[k].status & 0xFF) == CH_FAIL && !(fin == FIN_YES && o[k].has_eob)) { ok = false; break; }
+      const bool ends_here = fin == FIN_YES && k != 0 && o[k].has_eob;       // its first block was the last one
+      if (fin == FIN_YES && k != 0 && !o[k].has_eob && o[k].status != CH_LINKED) { ok = false; break; }
+      const uint32_t bytes = ends_here ? o[k].eob_bytes : o[k].out_bytes;
+      chain.push_back({i, k, total, bytes, ends_here ? o[k].eob_ntok : o[k].ntok, k == 0 ? (uint32_t)FIN_NO : fin, ends_here});
       off.push_back(total);
-      total += o[k].out_bytes;
+      total += bytes;
       if (total > in[i].dstlen || total > 0xFFFFFFFFull) { ok = false; break; }
+      if (ends_here) { end_bit[i] = o[k].eob_bit; break; }
       if (o[k].status == CH_FINAL) { end_bit[i] = o[k].end_bit; break; }
-      if (o[k].link <= k || o[k].link >= sd[i].ncand) { ok = false; break; }
+      if (o[k].status != CH_LINKED || o[k].link <= k || o[k].link >= sd[i].ncand) { ok = false; break; }
+      if (o[k].link_final != FIN_UNKNOWN) fin = o[k].link_final;            // else: still inside the same block
       k = o[k].link;
     }
     // markers index the 32 KiB before a chunk: they must exist
@@ -492,15 +520,15 @@ int split_decode_many(Engine* E, const SplitInput* in, size_t nin, int flags, vo
   std::vector<uint32_t> perm(nchunk);
   std::iota(perm.begin(), perm.end(), 0u);
   auto out_of = [&](uint32_t c) -> const SplitChunkOut& { return outs[sd[chain[c].stream].cand_base + chain[c].cand]; };
-  std::stable_sort(perm.begin(), perm.end(), [&](uint32_t a, uint32_t b) { return out_of(a).out_bytes > out_of(b).out_bytes; });
+  std::stable_sort(perm.begin(), perm.end(), [&](uint32_t a, uint32_t b) { return chain[a].bytes > chain[b].bytes; });
   for (uint32_t j = 0; j < nchunk; j++) {
     const ChainItem& ci = chain[perm[j]];
     const SplitStreamDesc& d = sd[ci.stream];
-    jobs[j].stream = ci.stream; jobs[j].pad = 0; jobs[j].cand = ci.cand;
-    jobs[j].cap = out_of(perm[j]).out_bytes; jobs[j].out_off = d.sym_base + ci.off;
+    jobs[j].stream = ci.stream; jobs[j].start_final = ci.start_final; jobs[j].cand = ci.cand;
+    jobs[j].cap = ci.bytes; jobs[j].out_off = d.sym_base + ci.off;
     jobs[j].tok_off = d.tok_base + (uint64_t)tok_per_byte * (cand[d.cand_base + ci.cand] >> 3);
     jobs[j].tok_cap = 0;
-    jobs[j].ntok = d_tok ? out_of(perm[j]).ntok : kNoTokens;
+    jobs[j].ntok = d_tok ? ci.ntok : kNoTokens;
   }
   if (SB.d_sym.reserve((size_t)sym_total * 2 + 64) || SB.d_off.reserve(off.size() * 8) ||
       SB.d_wbuf.reserve((size_t)win_total * kWinBytes + 64) || SB.d_partial.reserve((size_t)blk_total * 8 + 8) ||
@@ -546,11 +574,13 @@ int split_decode_many(Engine* E, const SplitInput* in, size_t nin, int flags, vo
   // the decode pass must have reproduced the count pass (it cannot differ for a deterministic decode; the
   // one-warp decoder has the last word if it ever does)
   for (uint32_t j = 0; j < nchunk; j++) {
+    const ChainItem& ci = chain[perm[j]];
     const SplitChunkOut& a = out_of(perm[j]);
-    const bool same = outs2[j].status == CH_REPLAYED
-                          ? outs2[j].out_bytes == a.out_bytes
-                          : (outs2[j].status == a.status && outs2[j].out_bytes == a.out_bytes && outs2[j].end_bit == a.end_bit);
-    if (!same) alive[chain[perm[j]].stream] = 0;
+    bool same;
+    if (outs2[j].status == CH_REPLAYED) same = outs2[j].out_bytes == ci.bytes;
+    else if (ci.ends) same = outs2[j].status == CH_FINAL && outs2[j].out_bytes == ci.bytes && outs2[j].end_bit == a.eob_bit;
+    else same = outs2[j].status == a.status && outs2[j].out_bytes == a.out_bytes && outs2[j].end_bit == a.end_bit;
+    if (!same) alive[ci.stream] = 0;
   }
   for (uint32_t i = 0; i < ns; i++) {
     if (!alive[i]) continue;
@@ -596,7 +626,7 @@ int split_decode_device(Engine* E, const uint8_t* d_src, uint64_t srclen, uint8_
 
 // Which streams of a batch go through the split decoder: the very large ones always; in a batch, those whose
 // one-warp decode would outlast the rest of the batch (bytes x resident warps > half the batch's bytes).
-static const uint64_t kSplitMinInBatch = 256ull << 10;    // compressed bytes below which splitting never pays
+static const uint64_t kSplitMinInBatch = 192ull << 10;    // compressed bytes below which splitting never pays
 bool wants_split(const infl_batch_item_t& it, uint64_t batch_bytes, uint64_t resident_warps) {
   if (it.srclen > 0xFFFFFFFFull || it.dstlen > 0xFFFFFFFFull) return false;
   if (it.srclen >= kSplitMinBytes) return true;
@@ -852,7 +882,11 @@ int run_device_batch(const infl_batch_item_t* items, size_t n, int flags, infl_b
                          rest.size(), flags, static_cast<infl_batch_result_t*>(E->d_results.p), E->d_ws.p, st) != UNZ_OK)
       return UNZ_ERR;
     CU_TRY(cudaMemcpyAsync(rr.data(), E->d_results.p, rr.size() * sizeof(rr[0]), cudaMemcpyDeviceToHost, st), "D2H results");
+    const auto t0 = std::chrono::steady_clock::now();
     CU_TRY(cudaStreamSynchronize(st), "inflate kernel");
+    if (std::getenv("DEFL_SPLIT_TRACE"))
+      std::fprintf(stderr, "[split] warp-per-stream kernel, %zu streams (%zu sent back by the split path) %8.3f ms\n", rest.size(),
+                   rest.size() - (n - sin.size()), std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count());
     for (size_t k = 0; k < rr.size(); k++) results[rest_idx[k]] = rr[k];
     return UNZ_OK;
   }

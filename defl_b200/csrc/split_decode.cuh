@@ -32,7 +32,15 @@ struct SplitChunkOut {
   uint32_t link;        // CH_LINKED: index of the candidate at end_bit
   uint32_t out_bytes;   // bytes the chunk produces
   uint32_t ntok;        // COUNT: tokens kept for the DECODE pass, or kNoTokens
+  // chunks that start INSIDE a block (mid-block mode) do not know whether that block is the stream's last one:
+  uint32_t link_final;  // CH_LINKED inside a block: 0 / 1 = that block is not / is final, 2 = as this chunk's first block
+  uint32_t has_eob;     // the chunk's first block (header unseen) ended inside it; if it was final, the chunk is:
+  uint32_t eob_bytes;   //   bytes produced up to there
+  uint32_t eob_ntok;    //   tokens kept up to there (or kNoTokens)
+  uint64_t eob_bit;     //   stream-relative bit after its end-of-block code
 };
+enum : uint32_t { FIN_NO = 0, FIN_YES = 1, FIN_UNKNOWN = 2 };
+enum : uint32_t { MODE_BLOCK_STARTS = 0, MODE_FIXED_MID = 1 };   // SplitStreamDesc::mode: what the candidates are
 
 // One stream of a split decode.  All the kernels below work on MANY streams at once: a table of these plus
 // cumulative bases (granules, candidates, chunks, windows, D2 blocks) says which stream a unit belongs to.
@@ -50,7 +58,8 @@ struct SplitStreamDesc {
   uint32_t off_base, nchunk;   // chain chunks: off[off_base .. off_base + nchunk] = output offsets
   uint32_t win_base;           // first of the stream's nchunk - 1 resolved windows in wbuf
   uint32_t nblk;               // D2 blocks
-  uint32_t pad;
+  uint32_t mode;               // MODE_*: candidates are block starts (found by F) or token boundaries inside
+                               // fixed-Huffman blocks (found by P; every candidate but the first)
 };
 
 // the stream that owns unit x: the last one whose base is <= x (streams without units share their successor's base)
@@ -63,7 +72,7 @@ DEFL_DEV uint32_t stream_of(uint32_t nstreams, uint64_t x, F base_of) {
 
 struct SplitJob {
   uint32_t stream;      // index into the stream table
-  uint32_t pad;
+  uint32_t start_final; // mid-block chunks: FIN_* of the block the chunk starts in (COUNT: FIN_UNKNOWN)
   uint32_t cand;        // index into the stream's candidates: where the chunk starts
   uint32_t cap;         // DECODE: exactly the bytes the COUNT pass reported
   uint64_t out_off;     // DECODE: offset of the chunk's first symbol
@@ -100,7 +109,9 @@ template <typename SYM, bool COUNT>
 DEFL_DEV void inflate_chunk_warp(WarpSmem& sm, const WarpScratch& sc, int lane, const uint8_t* src, uint32_t srclen,
                                  const uint64_t* cand, uint32_t ncand, uint32_t me, SYM* dst, uint32_t cap,
                                  uint32_t hist, SplitChunkOut& out, TokSink* sink = nullptr,
-                                 const uint32_t* saved = nullptr, uint32_t nsaved = kNoTokens) {
+                                 const uint32_t* saved = nullptr, uint32_t nsaved = kNoTokens,
+                                 uint32_t mode = MODE_BLOCK_STARTS, uint32_t start_final = FIN_UNKNOWN) {
+  out.link_final = FIN_NO; out.has_eob = 0; out.eob_bytes = 0; out.eob_ntok = kNoTokens; out.eob_bit = 0;
   if (!COUNT && saved && nsaved != kNoTokens) {
     // the COUNT pass kept this chunk's tokens: only the byte-producing half of the work is left
     uint32_t p = 0;
@@ -120,20 +131,27 @@ DEFL_DEV void inflate_chunk_warp(WarpSmem& sm, const WarpScratch& sc, int lane, 
   br.wend = (uint32_t)(((uint64_t)mis + srclen + 3u) >> 2);
   const uint64_t start = cand[me];
   br.seek(base_bit + start);
+  const bool mid = mode == MODE_FIXED_MID;          // candidates (but the first) are token boundaries inside fixed blocks
+  bool       in_first_unseen = mid && me != 0u;     // the chunk starts inside a block whose header it never saw
 
   uint32_t pos = 0, reason = R_NONE, next = me + 1u, status = CH_FAIL;
   bool     fixed_ready = false;
 #pragma unroll 1
   for (;;) {
-    const uint64_t q = br.bitpos() - base_bit;
-    if (q != start) {
-      while (next < ncand && cand[next] < q) next++;
-      if (next < ncand && cand[next] == q) { status = CH_LINKED; break; }
+    uint32_t bfinal, btype;
+    if (in_first_unseen) {
+      bfinal = start_final; btype = 1u;
+    } else {
+      const uint64_t q = br.bitpos() - base_bit;
+      if (!mid && q != start) {
+        while (next < ncand && cand[next] < q) next++;
+        if (next < ncand && cand[next] == q) { status = CH_LINKED; break; }
+      }
+      if ((int64_t)(end_bit - br.bitpos()) < 3) { reason = R_TRUNCATED; break; }
+      const uint32_t hdr = br.peek();
+      bfinal = hdr & 1u; btype = (hdr >> 1) & 3u;
+      br.skip(3); br.norm();
     }
-    if ((int64_t)(end_bit - br.bitpos()) < 3) { reason = R_TRUNCATED; break; }
-    const uint32_t hdr    = br.peek();
-    const uint32_t bfinal = hdr & 1u, btype = (hdr >> 1) & 3u;
-    br.skip(3); br.norm();
     if (btype == 0) {
       if (sink) sink->ok = false;          // stored bytes are not tokens: such a chunk decodes again
       reason = stored_block_sym<SYM, COUNT>(lane, br, src, srclen, base_bit, dst, pos, cap);
@@ -148,12 +166,37 @@ DEFL_DEV void inflate_chunk_warp(WarpSmem& sm, const WarpScratch& sc, int lane, 
       simt::syncwarp(kFull);
       uint64_t cur = br.bitpos();
       uint32_t st;
+      bool     linked = false;
 #pragma unroll 1
       do {
-        st = decode_window<SYM, COUNT>(sm, sc, lane, br.w, br.wend, end_bit, cur, dst, cap, pos, hist, sink);
+        uint64_t soft = ~0ull;
+        if (mid && btype == 1u) {
+          // inside a fixed block a later candidate may lie on this chunk's trajectory: stop exactly there
+          const uint64_t q = cur - base_bit;
+          while (next < ncand && cand[next] < q) next++;
+          if (next < ncand && cand[next] == q && q != start) { linked = true; break; }
+          if (next < ncand && cand[next] == q) next++;        // the chunk's own start
+          if (next < ncand) soft = base_bit + cand[next];
+        }
+        st = decode_window<SYM, COUNT>(sm, sc, lane, br.w, br.wend, end_bit, cur, dst, cap, pos, hist, sink, soft);
       } while (st == LS_OK);
+      if (linked) {
+        br.seek(cur);
+        status = CH_LINKED;
+        out.link_final = in_first_unseen ? start_final : bfinal;
+        break;
+      }
       if (st != LS_EOB) { reason = st >> 8; break; }
       br.seek(cur);
+    }
+    if (in_first_unseen) {
+      in_first_unseen = false;
+      if (bfinal == FIN_UNKNOWN) {
+        // remember where the chunk ends if that block was the last one, then go on as if it was not
+        out.has_eob = 1; out.eob_bytes = pos; out.eob_bit = br.bitpos() - base_bit;
+        out.eob_ntok = (COUNT && sink && sink->buf && sink->ok) ? sink->n : kNoTokens;
+        bfinal = 0;
+      }
     }
     if (bfinal) { status = CH_FINAL; break; }
   }
@@ -162,6 +205,35 @@ DEFL_DEV void inflate_chunk_warp(WarpSmem& sm, const WarpScratch& sc, int lane, 
   out.link      = next;
   out.out_bytes = pos;
   out.ntok      = (COUNT && sink && sink->buf && sink->ok) ? sink->n : kNoTokens;
+}
+
+// P: a probable token boundary inside a fixed-Huffman block, for one nominal chunk start (one LANE per chunk).
+// Decodes serially from bit p (an arbitrary position) for probe_bits: fixed codes re-synchronise, so where this
+// trajectory stands then is very likely a boundary of the true one.  A wrong guess costs nothing: no chunk's true
+// trajectory will land on it.  Stops (no candidate) at a final block, at any block that is not fixed, on any error.
+// lit / dist: the fixed-code tables.  Returns the absolute bit position or kNoCandidate.
+constexpr uint64_t kNoCandidate = ~0ull;
+DEFL_DEV uint64_t fixed_probe_lane(const uint16_t* lit, const uint16_t* dist, const uint32_t* words, uint32_t wend,
+                                   uint64_t p, uint64_t end_bit, uint32_t probe_bits) {
+  if (p + probe_bits + 64u >= end_bit) return kNoCandidate;
+  SubReader br;
+  br.w = words; br.wend = wend;
+  br.seek((uint32_t)(p >> 5), (uint32_t)(p & 31u));
+  uint64_t r = p;
+  const uint64_t target = p + probe_bits;
+#pragma unroll 1
+  for (;;) {
+    if (r >= target) return r;
+    uint32_t tok, used;
+    const uint64_t left = end_bit - r;
+    const uint32_t s = decode_token(lit, dist, br, left > 0x7FFFFFFFull ? 0x7FFFFFFFu : (uint32_t)left, false, tok, used);
+    if (s == LS_OK) { r += used; br.consume(used); continue; }
+    if (s != LS_EOB) return kNoCandidate;
+    r += used; br.consume(used);
+    const uint32_t hdr = simt::funnel_r(br.w0, br.w1, br.bo) & 7u;       // BFINAL, BTYPE of the next block
+    if ((hdr & 1u) || ((hdr >> 1) & 3u) != 1u) return kNoCandidate;
+    r += 3u; br.consume(3u);
+  }
 }
 
 #ifdef __CUDACC__
@@ -190,13 +262,48 @@ split_chunk_kernel(const SplitStreamDesc* __restrict__ streams, const uint64_t* 
     inflate_chunk_warp<uint16_t, COUNT>(sm, sc, lane, sd.src, (uint32_t)sd.srclen, cand + sd.cand_base, sd.ncand, job.cand,
                                         COUNT ? nullptr : sym + job.out_off, COUNT ? 0xFFFFFFFFu : job.cap,
                                         job.cand == 0u ? 0u : 32768u, o, COUNT ? &sink : nullptr,
-                                        (!COUNT && tokbuf) ? tokbuf + job.tok_off : nullptr, job.ntok);
+                                        (!COUNT && tokbuf) ? tokbuf + job.tok_off : nullptr, job.ntok,
+                                        sd.mode, job.start_final);
     if (lane == 0) outs[k] = o;
     simt::syncwarp(kFull);
   }
 }
 
-// first two bytes of every stream (zlib header check on the host) / the four bytes at a given offset (Adler trailer)
+// P for every granule of the streams in MODE_FIXED_MID: one lane per granule, the warp's fixed-code tables shared
+template <int WARPS>
+__global__ void __launch_bounds__(WARPS * 32)
+fixed_probe_kernel(const SplitStreamDesc* __restrict__ streams, uint32_t nstreams, uint32_t ngran_total,
+                   uint32_t granule_bytes, uint32_t probe_bits, uint64_t* __restrict__ found) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  WarpSmem& sm = reinterpret_cast<WarpSmem*>(smem_raw)[warp];
+  Lane<32> L;
+  L.gmask = kFull; L.lane = lane; L.wlane = lane;
+  BitReader none;
+  none.w = nullptr; none.wend = 0;
+  bool fixed_ready = false;
+  huffman_block_setup<32>(L, sm.lit, sm.dist, sm.s, none, 0, 1u, fixed_ready);
+  simt::syncwarp(kFull);
+  const uint32_t gg = (blockIdx.x * WARPS + warp) * 32u + (uint32_t)lane;
+  if (gg >= ngran_total) return;
+  const SplitStreamDesc& sd = streams[stream_of(nstreams, gg, [&](uint32_t i) { return (uint64_t)streams[i].gran_base; })];
+  if (sd.mode != MODE_FIXED_MID) return;
+  const uint32_t g = gg - sd.gran_base;
+  uint64_t result = kNoCandidate;
+  if (g != 0u) {                                            // granule 0 starts the stream: a known block start
+    const uint32_t mis      = (uint32_t)((uintptr_t)sd.src & 3u);
+    const uint64_t base_bit = (uint64_t)mis * 8u;
+    const uint64_t end_bit  = base_bit + sd.srclen * 8u;
+    const uint32_t* words   = reinterpret_cast<const uint32_t*>((uintptr_t)sd.src - mis);
+    const uint32_t  wend    = (uint32_t)(((uint64_t)mis + sd.srclen + 3u) >> 2);
+    const uint64_t  p       = base_bit + ((uint64_t)sd.body + (uint64_t)g * granule_bytes) * 8u;
+    const uint64_t  r       = fixed_probe_lane(sm.lit, sm.dist, words, wend, p, end_bit, probe_bits);
+    if (r != kNoCandidate) result = r - base_bit;
+  }
+  found[gg] = result;
+}
+
+// first bytes of every stream (zlib header check, first block type, on the host) / the four bytes at a given offset (Adler trailer)
 __global__ void split_peek_kernel(const SplitStreamDesc* __restrict__ streams, uint32_t nstreams,
                                   const uint64_t* __restrict__ at, uint32_t nbytes, uint8_t* __restrict__ out) {
   const uint32_t s = blockIdx.x * blockDim.x + threadIdx.x;
@@ -209,7 +316,6 @@ __global__ void split_peek_kernel(const SplitStreamDesc* __restrict__ streams, u
 #endif  // __CUDACC__
 
 // ---- F: block-start search -------------------------------------------------------------------------------
-constexpr uint64_t kNoCandidate = ~0ull;
 
 // The search is a funnel, every stage lane-parallel over bit positions (nothing here is warp-serial):
 //   1. cheap   : BTYPE = dynamic, HLIT <= 286, HDIST <= 30                       (22 % of positions pass)
@@ -366,6 +472,7 @@ find_block_starts_kernel(const SplitStreamDesc* __restrict__ streams, uint32_t n
   const uint32_t gg = blockIdx.x * WARPS + warp;          // granule number over all streams
   if (gg >= ngran_total) return;
   const SplitStreamDesc& sd = streams[stream_of(nstreams, gg, [&](uint32_t i) { return (uint64_t)streams[i].gran_base; })];
+  if (sd.mode != MODE_BLOCK_STARTS) return;               // P fills this stream's entries
   const uint8_t* const src = sd.src;
   const uint32_t srclen = (uint32_t)sd.srclen, body = sd.body;
   const uint32_t g = gg - sd.gran_base;

@@ -489,19 +489,24 @@ struct TokSink {
 template <typename SYM, bool COUNT>
 DEFL_DEV uint32_t decode_window(WarpSmem& sm, const WarpScratch& sc, int lane, const uint32_t* words,
                                 uint32_t wend, uint64_t end_bit, uint64_t& cur, SYM* dst, uint32_t cap,
-                                uint32_t& pos, uint32_t hist, TokSink* sink = nullptr) {
+                                uint32_t& pos, uint32_t hist, TokSink* sink = nullptr,
+                                uint64_t soft_end = ~0ull) {
+  // soft_end (> cur): no token that STARTS at or after this bit is decoded in this window, so the window ends on
+  // the first token boundary >= soft_end (the caller compares `cur` with it: split decode links chunks there)
   const uint32_t bw   = (uint32_t)(cur >> 5);
   const uint32_t rel0 = (uint32_t)(cur & 31u);
   const uint64_t left64 = end_bit - ((uint64_t)bw << 5);
   const uint32_t endr = left64 > 0x40000000ull ? 0x40000000u : (uint32_t)left64;   // window-relative end of input
-  const uint32_t remaining = endr - rel0;
+  const uint64_t soft64 = soft_end == ~0ull ? ~0ull : soft_end - ((uint64_t)bw << 5);
+  const uint32_t softr = soft64 > (uint64_t)endr ? endr : (uint32_t)soft64;        // window-relative soft end
+  const uint32_t remaining = softr - rel0;
   uint32_t S = (remaining + 31u) / 32u;
   S = (S + kCpBits - 1u) / kCpBits * kCpBits;
   S = S < kSubMin ? kSubMin : (S > kSubMax ? kSubMax : S);
 
   const uint32_t start = rel0 + (uint32_t)lane * S;
-  const uint32_t limit = start + S;
-  const bool     active = start < endr || lane == 0;
+  const uint32_t limit = (soft_end != ~0ull && start + S > softr) ? softr : start + S;
+  const bool     active = start < softr || lane == 0;
   uint32_t* seg = sc.spec + (uint32_t)lane * kSpecCap;
   uint32_t* fix = sc.fix + (uint32_t)lane * kFixCap;
   uint16_t* cps = sc.cps + (uint32_t)lane * kCpPerLane;
