@@ -178,7 +178,8 @@ DEFL_DEV void inflate_chunk_warp(WarpSmem& sm, const WarpScratch& sc, int lane, 
           if (next < ncand && cand[next] == q) next++;        // the chunk's own start
           if (next < ncand) soft = base_bit + cand[next];
         }
-        st = decode_window<SYM, COUNT>(sm, sc, lane, br.w, br.wend, end_bit, cur, dst, cap, pos, hist, sink, soft);
+        st = decode_window<SYM, COUNT>(sm, sc, lane, br.w, br.wend, end_bit, cur, dst, cap, pos, hist, sink, soft,
+                                       btype == 1u ? kWarmFixed : kWarmDynamic);
       } while (st == LS_OK);
       if (linked) {
         br.seek(cur);

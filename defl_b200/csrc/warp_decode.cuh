@@ -34,6 +34,14 @@ constexpr uint32_t kFixCap    = 1024;                 // tokens per lane per win
 constexpr size_t   kWarpScratchBytes = 32u * (kSpecCap + kFixCap) * 4u + 32u * kCpPerLane * 2u;
 static_assert(kWarpScratchBytes % 16 == 0, "scratch slices stay 16-byte aligned");
 
+#ifndef DEFL_WARM_DYNAMIC
+#define DEFL_WARM_DYNAMIC 512
+#endif
+#ifndef DEFL_WARM_FIXED
+#define DEFL_WARM_FIXED 4096
+#endif
+constexpr uint32_t kWarmDynamic = DEFL_WARM_DYNAMIC;  // bits a lane decodes ahead of its sub-sequence to get in step (dynamic codes)
+constexpr uint32_t kWarmFixed   = DEFL_WARM_FIXED;    // fixed-Huffman codes are nearly fixed-length and re-synchronise slowly
 constexpr int      kStageV3   = 512;                  // output bytes resolved per token batch
 constexpr uint32_t kTokIsMatch = 0x80000000u;         // [8:0] length, [23:9] distance - 1
 constexpr uint32_t kTokIsDep   = 0x40000000u;         // resolver-side mark
@@ -147,11 +155,31 @@ struct LaneTraj {
 // running pointers for the token and checkpoint stores.
 DEFL_DEV void lane_spec(const uint16_t* lit, const uint16_t* dist, const uint32_t* words, uint32_t wend,
                         uint32_t bw, uint32_t start, uint32_t limit, uint32_t endr, uint32_t* seg,
-                        uint16_t* cps, LaneTraj& tj) {
+                        uint16_t* cps, LaneTraj& tj, uint32_t warm) {
   SubReader br;
   br.w = words; br.wend = wend;
-  br.seek(bw, start);
-  uint32_t        r = start, next_cp = start, stat = LS_OK;
+  uint32_t r = start;
+  if (warm) {
+    // Warm-up: start `warm` bits early and throw the tokens away.  Codes self-synchronise, so by the time the
+    // lane reaches its sub-sequence it is most likely ON the true trajectory and its first kept token starts
+    // exactly where its predecessor will end: no fix-up needed.  If the warm-up runs into anything that is not
+    // a token (end of block, no code) the lane starts blind at `start`, as it would have without it.
+    uint32_t q = start - warm;
+    br.seek(bw, q);
+    bool ok = true;
+#pragma unroll 1
+    while (q < start) {
+      uint32_t tok, used;
+      if (decode_token(lit, dist, br, endr > q ? endr - q : 0u, false, tok, used) != LS_OK) { ok = false; break; }
+      q += used;
+      br.consume(used);
+    }
+    if (ok) r = q; else br.seek(bw, start);
+  } else {
+    br.seek(bw, start);
+  }
+  const uint32_t  r0 = r;
+  uint32_t        next_cp = start, stat = LS_OK;
   uint32_t*       tp = seg;
   uint32_t* const tend = seg + kSpecCap;
   uint16_t*       cpp = cps;
@@ -210,7 +238,7 @@ DEFL_DEV void lane_spec(const uint16_t* lit, const uint16_t* dist, const uint32_
     br.consume(used);
   }
   const uint32_t t = (uint32_t)(tp - seg);
-  tj.land = r; tj.stat = stat; tj.n = t; tj.m = 0; tj.nf = 0; tj.T = start; tj.ncp = (uint32_t)(cpp - cps);
+  tj.land = r; tj.stat = stat; tj.n = t; tj.m = 0; tj.nf = 0; tj.T = r0; tj.ncp = (uint32_t)(cpp - cps);
   tj.s_land = r; tj.s_stat = stat; tj.s_n = t;
 }
 
@@ -279,7 +307,10 @@ DEFL_DEV void lane_redo(const uint16_t* lit, const uint16_t* dist, const uint32_
 template <typename SYM> struct SymWord;
 template <> struct SymWord<uint8_t>  { static constexpr uint32_t kPer = 4, kShift = 2, kBits = 8,  kMask = 0xFFu; };
 template <> struct SymWord<uint16_t> { static constexpr uint32_t kPer = 2, kShift = 1, kBits = 16, kMask = 0xFFFFu; };
-constexpr uint32_t kLaneWords = 4;      // a lane copies matches of up to this many words' worth of symbols itself
+#ifndef DEFL_LANE_WORDS
+#define DEFL_LANE_WORDS 4
+#endif
+constexpr uint32_t kLaneWords = DEFL_LANE_WORDS;      // a lane copies matches of up to this many words' worth of symbols itself
 
 template <typename SYM>
 DEFL_DEV uint32_t resolve_tokens(uint16_t* stage_mem, int lane, const uint32_t* toks, uint32_t count, SYM* dst0,
@@ -490,7 +521,7 @@ template <typename SYM, bool COUNT>
 DEFL_DEV uint32_t decode_window(WarpSmem& sm, const WarpScratch& sc, int lane, const uint32_t* words,
                                 uint32_t wend, uint64_t end_bit, uint64_t& cur, SYM* dst, uint32_t cap,
                                 uint32_t& pos, uint32_t hist, TokSink* sink = nullptr,
-                                uint64_t soft_end = ~0ull) {
+                                uint64_t soft_end = ~0ull, uint32_t warm_bits = kWarmDynamic) {
   // soft_end (> cur): no token that STARTS at or after this bit is decoded in this window, so the window ends on
   // the first token boundary >= soft_end (the caller compares `cur` with it: split decode links chunks there)
   const uint32_t bw   = (uint32_t)(cur >> 5);
@@ -514,7 +545,8 @@ DEFL_DEV uint32_t decode_window(WarpSmem& sm, const WarpScratch& sc, int lane, c
   LaneTraj tj;
   tj.land = start; tj.stat = LS_NONE; tj.n = 0; tj.m = 0; tj.nf = 0; tj.T = start; tj.ncp = 0;
   tj.s_land = start; tj.s_stat = LS_NONE; tj.s_n = 0;
-  if (active) lane_spec(sm.lit, sm.dist, words, wend, bw, start, limit, endr, seg, cps, tj);
+  const uint32_t warm = (lane >= 1 && active) ? (warm_bits < S ? warm_bits : S) : 0u;      // lane 0 starts on a known boundary
+  if (active) lane_spec(sm.lit, sm.dist, words, wend, bw, start, limit, endr, seg, cps, tj, warm);
   simt::syncwarp(kFull);
 
   // fix-up rounds until every lane starts where its predecessor ended
@@ -647,7 +679,8 @@ DEFL_DEV void inflate_stream_warp(WarpSmem& sm, const WarpScratch& sc, int lane,
       uint32_t st;
 #pragma unroll 1
       do {
-        st = decode_window<uint8_t, false>(sm, sc, lane, br.w, br.wend, end_bit, cur, dst, cap, pos, 0u);
+        st = decode_window<uint8_t, false>(sm, sc, lane, br.w, br.wend, end_bit, cur, dst, cap, pos, 0u, nullptr, ~0ull,
+                                           btype == 1u ? kWarmFixed : kWarmDynamic);
       } while (st == LS_OK);
       if (st != LS_EOB) { reason = st >> 8; break; }
       br.seek(cur);
