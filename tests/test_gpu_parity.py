@@ -410,3 +410,44 @@ def test_split_many_streams_in_one_batch(gpu_lib):
     exp = code if code != 0 else (0 if zlib.adler32(ol.port_inflate(bytes(bad), len(streams[0][0]), 1)[1]) else 0)
     assert (int(results[0]["code"]) == 0) == (code == 0 and int(results[0]["adler"]) == int(results[0]["adler_stored"]))
     assert all(int(g["code"]) == 0 for g in results[1:])
+
+
+@pytest.mark.gpu
+def test_split_paths_on_damaged_streams(gpu_lib):
+    """Mutants of large dynamic and fixed-Huffman streams through the device-resident batch call (they take the
+    split decoder, which hands anything it cannot finish to the one-warp decoder): per member the verdict, and for
+    accepted members the bytes / length / Adler-32, equal the oracle's."""
+    import torch
+    from defl_b200 import synth, api
+    d = gpu_lib
+    Z = zlib.Z_DEFAULT_STRATEGY
+    base = synth.make_streams([("text", 2 << 20, 31, 6, Z), ("png", 2 << 20, 32, 6, zlib.Z_FIXED),
+                               ("log", 3 << 20, 33, 6, zlib.Z_FIXED), ("text", 1500000, 34, 9, Z)], threads=4)
+    rng = np.random.default_rng(99)
+    cases = []
+    for raw, z in base:
+        cases.append((z, len(raw)))                                   # intact
+        cases.append((z[: len(z) * 2 // 3], len(raw)))               # truncated
+        cases.append((z, len(raw) - 1))                               # one byte short of output
+        for _ in range(4):                                            # bit flips anywhere in the body
+            b = bytearray(z)
+            pos = int(rng.integers(2, len(b) - 4))
+            b[pos] ^= 1 << int(rng.integers(0, 8))
+            cases.append((bytes(b), len(raw)))
+        b = bytearray(z); b[-1] ^= 0xFF                               # damaged Adler trailer
+        cases.append((bytes(b), len(raw)))
+    dev = torch.device("cuda", 0)
+    srcs = [torch.frombuffer(bytearray(z), dtype=torch.uint8).to(dev) for z, _ in cases]
+    dsts = [torch.zeros(cap + 8, dtype=torch.uint8, device=dev) for _, cap in cases]
+    items = np.zeros(len(cases), dtype=d.ITEM_DTYPE)
+    for i, ((z, cap), s, t) in enumerate(zip(cases, srcs, dsts)):
+        items[i] = (s.data_ptr(), len(z), t.data_ptr(), cap)
+    results = np.zeros(len(cases), dtype=d.RESULT_DTYPE)
+    api.infl_buf_batch_raw(items, d.INFL_ZLIB | d.INFL_BATCH_DEVICE_PTRS, results)     # reference semantics: no Adler veto
+    torch.cuda.synchronize()
+    for i, ((z, cap), t, g) in enumerate(zip(cases, dsts, results)):
+        code, want, r = ol.port_inflate(z, cap, 1)
+        assert int(g["code"]) == code, (i, int(g["code"]), code, int(g["info"]))
+        if code == 0:
+            assert int(g["outlen"]) == len(want) and int(g["adler"]) == r.adler, i
+            assert t[: len(want)].cpu().numpy().tobytes() == want, i
