@@ -495,9 +495,12 @@ def main():
                 "algorithmic_bytes_per_launch": in_bytes + out_bytes,
                 "kernel_ms": kern_ms}
     prof = os.path.join(ROOT, "profiles", "traffic.json")
-    if os.path.exists(prof):
+    if os.path.exists(prof) and not args.lanes and args.engine in (0, 3):
         try:
-            roofline["traffic"] = json.load(open(prof)).get("inflate_batch_kernel_bytes_per_launch")
+            tj = json.load(open(prof))
+            roofline["traffic"] = float(tj["dram_bytes_over_algorithmic_bytes"]) * (in_bytes + out_bytes)
+            roofline["traffic_source"] = "ncu dram bytes / algorithmic bytes = %.2f at 16000 streams per launch (%s), scaled to this launch" % (
+                tj["dram_bytes_over_algorithmic_bytes"], "profiles/r01_v3c_ncu_full_summary.json")
         except Exception:
             pass
 
