@@ -315,9 +315,9 @@ int split_decode_many(Engine* E, const SplitInput* in, size_t nin, int flags, vo
   };
   static const uint32_t granule = env_u32("DEFL_SPLIT_GRANULE", 32768u, 4096u, 1u << 24);
   static const uint64_t min_gap = (uint64_t)env_u32("DEFL_SPLIT_GAP", 40960u, 0u, 1u << 28) * 8u;   // bits
-  static const uint32_t tok_per_byte = env_u32("DEFL_SPLIT_TOKENS_PER_BYTE", 2u, 0u, 32u);
+  static const uint32_t tok_per_byte = env_u32("DEFL_SPLIT_TOKENS_PER_BYTE", 3u, 0u, 32u);
   static const bool     fixed_mid = env_u32("DEFL_SPLIT_FIXED", 1u, 0u, 1u) != 0u;
-  static const uint32_t probe_bits = env_u32("DEFL_SPLIT_PROBE_BITS", 8192u, 256u, 1u << 20);
+  static const uint32_t probe_bits = env_u32("DEFL_SPLIT_PROBE_BITS", 16384u, 256u, 1u << 20);
 
   int grid_warps = 0;
   if (warp_kernel_grid(E->sms, &grid_warps) != UNZ_OK) return UNZ_ERR;      // CTAs of kWarpsPerCta warps
@@ -432,6 +432,23 @@ int split_decode_many(Engine* E, const SplitInput* in, size_t nin, int flags, vo
         jobs[j].ntok = kNoTokens;
       }
   }
+  // longest chunk first (fixed-Huffman chunks count double: they decode slowly): the pass ends when its slowest
+  // warp does.  outs[] stays in candidate order: a_slot[j] says which record job j fills.
+  std::vector<uint32_t> a_order(ncand);
+  std::iota(a_order.begin(), a_order.end(), 0u);
+  {
+    std::vector<uint64_t> w(ncand);
+    for (uint32_t j = 0; j < ncand; j++) {
+      const SplitStreamDesc& d = sd[jobs[j].stream];
+      const uint64_t* c = cand.data() + d.cand_base;
+      const uint64_t e = jobs[j].cand + 1 < d.ncand ? c[jobs[j].cand + 1] : in[jobs[j].stream].srclen * 8;
+      w[j] = (e - c[jobs[j].cand]) * (d.mode == MODE_FIXED_MID ? 2u : 1u);
+    }
+    std::stable_sort(a_order.begin(), a_order.end(), [&](uint32_t a, uint32_t b) { return w[a] > w[b]; });
+    std::vector<SplitJob> sorted(ncand);
+    for (uint32_t j = 0; j < ncand; j++) sorted[j] = jobs[a_order[j]];
+    jobs.swap(sorted);
+  }
   if (SB.d_cand.reserve((size_t)ncand * 8) || SB.d_jobs.reserve((size_t)ncand * sizeof(SplitJob)) ||
       SB.d_outs.reserve((size_t)ncand * sizeof(SplitChunkOut)) || SB.d_outs2.reserve((size_t)ncand * sizeof(SplitChunkOut)) ||
       upload_streams() != UNZ_OK)
@@ -461,8 +478,12 @@ int split_decode_many(Engine* E, const SplitInput* in, size_t nin, int flags, vo
   };
   if (launch_chunks(true, ncand, nullptr) != UNZ_OK) return UNZ_ERR;
   std::vector<SplitChunkOut> outs(ncand);
-  CU_TRY(cudaMemcpyAsync(outs.data(), SB.d_outs.p, (size_t)ncand * sizeof(SplitChunkOut), cudaMemcpyDeviceToHost, st), "D2H chunk sizes");
-  CU_TRY(cudaStreamSynchronize(st), "split_chunk_kernel (count)");
+  {
+    std::vector<SplitChunkOut> by_job(ncand);
+    CU_TRY(cudaMemcpyAsync(by_job.data(), SB.d_outs.p, (size_t)ncand * sizeof(SplitChunkOut), cudaMemcpyDeviceToHost, st), "D2H chunk sizes");
+    CU_TRY(cudaStreamSynchronize(st), "split_chunk_kernel (count)");
+    for (uint32_t j = 0; j < ncand; j++) outs[a_order[j]] = by_job[j];      // back to candidate order
+  }
   mark("A count pass");
 
   // ---- per stream, the chain of true chunks from its first block to its final block
@@ -520,7 +541,11 @@ int split_decode_many(Engine* E, const SplitInput* in, size_t nin, int flags, vo
   std::vector<uint32_t> perm(nchunk);
   std::iota(perm.begin(), perm.end(), 0u);
   auto out_of = [&](uint32_t c) -> const SplitChunkOut& { return outs[sd[chain[c].stream].cand_base + chain[c].cand]; };
-  std::stable_sort(perm.begin(), perm.end(), [&](uint32_t a, uint32_t b) { return chain[a].bytes > chain[b].bytes; });
+  // a replayed chunk costs about its tokens, a re-decoded one (no kept tokens) about its bytes
+  auto c_weight = [&](uint32_t c) -> uint64_t {
+    return chain[c].ntok != kNoTokens ? (uint64_t)chain[c].ntok * 4u + chain[c].bytes / 4u : (uint64_t)chain[c].bytes * 2u;
+  };
+  std::stable_sort(perm.begin(), perm.end(), [&](uint32_t a, uint32_t b) { return c_weight(a) > c_weight(b); });
   for (uint32_t j = 0; j < nchunk; j++) {
     const ChainItem& ci = chain[perm[j]];
     const SplitStreamDesc& d = sd[ci.stream];
@@ -538,7 +563,15 @@ int split_decode_many(Engine* E, const SplitInput* in, size_t nin, int flags, vo
   CU_TRY(cudaMemcpyAsync(SB.d_off.p, off.data(), off.size() * 8, cudaMemcpyHostToDevice, st), "H2D offsets");
   if (launch_chunks(false, nchunk, static_cast<uint16_t*>(SB.d_sym.p)) != UNZ_OK) return UNZ_ERR;
   mark("C decode pass");
-  if (trace) std::fprintf(stderr, "[split] streams %u ncand %u nchunk %u symbols %llu\n", ns, ncand, nchunk, (unsigned long long)sym_total);
+  if (trace) {
+    uint64_t nre = 0, bre = 0, nfx = 0;
+    for (uint32_t c = 0; c < nchunk; c++) {
+      if (chain[c].ntok == kNoTokens) { nre++; bre += chain[c].bytes; if (sd[chain[c].stream].mode == MODE_FIXED_MID) nfx++; }
+    }
+    std::fprintf(stderr, "[split] streams %u ncand %u nchunk %u symbols %llu; decoded again (tokens not kept): %llu chunks "
+                 "(%llu in fixed-Huffman streams), %llu bytes\n", ns, ncand, nchunk, (unsigned long long)sym_total,
+                 (unsigned long long)nre, (unsigned long long)nfx, (unsigned long long)bre);
+  }
   std::vector<SplitChunkOut> outs2(nchunk);
   CU_TRY(cudaMemcpyAsync(outs2.data(), SB.d_outs2.p, (size_t)nchunk * sizeof(SplitChunkOut), cudaMemcpyDeviceToHost, st), "D2H chunk results");
 
