@@ -47,7 +47,8 @@ def parse():
     ap.add_argument("--mixed-gib", type=float, default=8.0, help="mixed workload: decompressed GiB per GPU")
     ap.add_argument("--mixed-no-fixed", action="store_true", help="mixed workload without the forced Z_FIXED streams (diagnosis)")
     ap.add_argument("--mixed-unique-mib", type=int, default=1024, help="mixed workload: distinct MiB generated on the host")
-    ap.add_argument("--workload", default="batch", choices=["batch", "single", "mixed"],
+    ap.add_argument("--chunk-streams", type=int, default=256, help="chunks workload: 4 MiB streams per step")
+    ap.add_argument("--workload", default="batch", choices=["batch", "single", "mixed", "chunks"],
                     help="batch = configs[1] (headline); single = configs[3], one large stream, split-point decode")
     ap.add_argument("--single-bytes", type=int, default=1 << 30)
     ap.add_argument("--e2e-steps", type=int, default=2)
@@ -258,6 +259,100 @@ def run_single(args, d, dev):
         "gpu_launches": int(launches)}))
 
 
+def run_chunks(args, d, dev):
+    """BASELINE.json configs[2]: 4 MiB streams (png and text, level 6) handed over as lists of pieces, never joined
+    on the host, through infl_buf_batch_iov (the batched infl_include).  Piece sizes follow SURVEY.md 8(d), driven by
+    the LCG of test_fuzz.c:139-142: (ii) half 1-16 B / half 1-32768 B, (iii) 8193-32192 B, and (i) all 1-byte pieces
+    on two streams only (4 M descriptors).  Host pieces in, host output out: the timed region holds H2D, the device
+    gather, the decode and D2H."""
+    import torch
+    from defl_b200 import synth, api
+    n = args.chunk_streams
+    Z = zlib.Z_DEFAULT_STRATEGY
+    t0 = time.time()
+    streams = synth.make_streams([("png" if i & 1 else "text", 4 << 20, 500 + i, 6, Z) for i in range(n)],
+                                 threads=os.cpu_count() or 1)
+    gen_s = time.time() - t0
+    raws, zs = [r for r, _ in streams], [z for _, z in streams]
+    src_h, so, sl = synth.pack(zs, align=1)
+    h_src = torch.from_numpy(src_h).pin_memory()
+    out_len = np.array([len(r) for r in raws], dtype=np.int64)
+    out_off = np.concatenate([[0], np.cumsum(out_len)])[:-1]
+    h_dst = torch.zeros(int(out_len.sum()), dtype=torch.uint8).pin_memory()
+    flags = d.INFL_ZLIB | d.INFL_BATCH_VERIFY_ADLER
+
+    def piece_sizes(kind, total, state):
+        sizes, left = [], total
+        if kind == "one":
+            return np.ones(total, dtype=np.int64), state
+        while left > 0:
+            state = (state * 1103515245 + 12345) & 0xFFFFFFFF
+            r = state >> 8
+            if kind == "mix":
+                k = 1 + r % 16 if (state >> 4) & 1 else 1 + r % 32768
+            else:
+                k = 8193 + r % 24000
+            k = min(k, left)
+            sizes.append(k)
+            left -= k
+        return np.array(sizes, dtype=np.int64), state
+
+    def run(kind, idx, steps):
+        state, iovs = 0x12345678, []
+        items = np.zeros(len(idx), dtype=api.IOV_ITEM_DTYPE)
+        npieces = 0
+        for j, i in enumerate(idx):
+            sizes, state = piece_sizes(kind, int(sl[i]), state)
+            iov = np.zeros(len(sizes), dtype=api.IOVEC_DTYPE)
+            iov["ptr"] = h_src.data_ptr() + int(so[i]) + np.concatenate([[0], np.cumsum(sizes)])[:-1]
+            iov["len"] = sizes
+            iovs.append(iov)
+            items[j] = (iov.ctypes.data, len(sizes), h_dst.data_ptr() + int(out_off[i]), int(out_len[i]))
+            npieces += len(sizes)
+        res = np.zeros(len(idx), dtype=d.RESULT_DTYPE)
+        call = lambda: d.lib().infl_buf_batch_iov(items.ctypes.data, len(idx), int(flags), res.ctypes.data)
+        assert call() == 0, d.last_error()                  # warm-up (allocates staging once)
+        h_dst.zero_()
+        torch.cuda.synchronize()
+        l0 = d.kernel_launch_count()
+        t = time.perf_counter()
+        for _ in range(steps):
+            assert call() == 0, d.last_error()
+        torch.cuda.synchronize()
+        dt = (time.perf_counter() - t) / steps
+        launches = (d.kernel_launch_count() - l0) // steps
+        assert (res["code"] == 0).all() and (res["adler"] == res["adler_stored"]).all()
+        hv = h_dst.numpy()
+        for i in idx:
+            assert hv[out_off[i]: out_off[i] + out_len[i]].tobytes() == raws[i], f"stream {i} differs"
+        outb = int(out_len[idx].sum())
+        return {"pieces_per_step": npieces, "streams": len(idx), "ms_per_step": dt * 1e3, "GBps": outb / dt / 1e9,
+                "h2d_bytes": int(sl[idx].sum()), "d2h_bytes": outb, "launches": int(launches)}
+
+    allidx = np.arange(n)
+    steps = max(args.steps, 1)
+    mix = run("mix", allidx, steps)
+    large = run("large", allidx, steps)
+    one = run("one", allidx[:2], 1)
+    peak, peak_src = peaks()
+    achieved = (mix["h2d_bytes"] * 2 + mix["h2d_bytes"] + mix["d2h_bytes"]) / (mix["ms_per_step"] / 1e3) / 1e9
+    print(json.dumps({
+        "metric": "decompressed GB/s, zlib streams given as chunk lists, host to host", "value": mix["GBps"], "unit": UNIT,
+        "n_gpus": 1, "steps": steps, "warmup": 1, "ms_per_step": mix["ms_per_step"], "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+        "config": {"workload": "configs[2]: 4 MiB streams (png / text, level 6) as lists of 1 B - 32 KiB pieces through "
+                               "infl_buf_batch_iov; value = chunking (ii)", "chunking_ii_mix": mix, "chunking_iii_8k_32k": large,
+                   "chunking_i_all_1_byte": one, "engine": d.engine_info(), "gen_seconds": round(gen_s, 1),
+                   "timing": "host clock around the call (host pieces in, host bytes out)"},
+        "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+                     "peak_source": peak_src, "kernel": "whole call (gather_pieces_kernel: 2 x pieces; decode: in + out)",
+                     "algorithmic_bytes_per_launch": mix["h2d_bytes"] * 3 + mix["d2h_bytes"]},
+        "cpu_baseline": None,
+        "e2e": {"value": mix["GBps"], "unit": UNIT, "h2d_bytes_per_step": mix["h2d_bytes"] + 16 * mix["pieces_per_step"],
+                "d2h_bytes_per_step": mix["d2h_bytes"]},
+        "gpu_launches": mix["launches"] * steps}))
+
+
 def run_mixed(args, d, dev, rank, world, local, dist):
     """BASELINE.json configs[4] shape: stored / fixed / dynamic blocks, levels 1/6/9, sizes log-uniform in
     [64 KiB, 4 MiB], classes text/log/png/rand/zero (synth.config5_specs).  Each GPU owns --mixed-gib GiB of
@@ -417,6 +512,9 @@ def main():
         return
     if args.workload == "mixed":
         run_mixed(args, d, dev, rank, world, local, dist)
+        return
+    if args.workload == "chunks":
+        run_chunks(args, d, dev)
         return
 
     n = args.streams

@@ -95,7 +95,7 @@ struct Engine {
   int          sms      = 0;
   cudaStream_t stream   = nullptr;
   std::mutex   mu;
-  DevBuf       d_in, d_out, d_items, d_results, d_order, d_ws, d_seg;
+  DevBuf       d_in, d_out, d_items, d_results, d_order, d_ws, d_seg, d_stage;
   PinBuf       h_items, h_results, h_order, h_pack, h_seg;
   bool         ready = false;
 };
@@ -866,10 +866,8 @@ int run_host_batch_on_device(const infl_batch_item_t* items, size_t n, int flags
 }
 
 // ---- device-pointer batch: only descriptors and results cross the bus ---------------------------------------
-int run_device_batch(const infl_batch_item_t* items, size_t n, int flags, infl_batch_result_t* results) {
-  Engine* E = nullptr;
-  if (engine_for_current_device(&E) != UNZ_OK) return UNZ_ERR;
-  std::lock_guard<std::mutex> guard(E->mu);
+// device-resident streams -> results (host array).  The engine's mutex is held by the caller.
+int run_device_batch_locked(Engine* E, const infl_batch_item_t* items, size_t n, int flags, infl_batch_result_t* results) {
   cudaStream_t st = E->stream;
   if (E->d_items.reserve(n * sizeof(infl_batch_item_t)) || E->d_results.reserve(n * sizeof(infl_batch_result_t)) ||
       E->d_order.reserve(n * sizeof(uint32_t)) || E->d_ws.reserve_exact(warp_kernel_workspace(E->sms)) ||
@@ -933,6 +931,13 @@ int run_device_batch(const infl_batch_item_t* items, size_t n, int flags, infl_b
   CU_TRY(cudaMemcpyAsync(results, E->d_results.p, n * sizeof(*results), cudaMemcpyDeviceToHost, st), "D2H results");
   CU_TRY(cudaStreamSynchronize(st), "inflate kernel");
   return UNZ_OK;
+}
+
+int run_device_batch(const infl_batch_item_t* items, size_t n, int flags, infl_batch_result_t* results) {
+  Engine* E = nullptr;
+  if (engine_for_current_device(&E) != UNZ_OK) return UNZ_ERR;
+  std::lock_guard<std::mutex> guard(E->mu);
+  return run_device_batch_locked(E, items, n, flags, results);
 }
 
 // ---- multi-GPU sharding of a host batch: byte-balanced, no collective ----------------------------
@@ -1140,36 +1145,62 @@ UNZ_EXPORT int infl_buf_batch_iov(const infl_batch_iov_item_t* items, size_t n, 
         if (infl_gather_device(ds_src, ds_len, ds_len + nseg, nseg, din, st) != UNZ_OK) return UNZ_ERR;
       }
     } else {
-      // DMA join; small pieces ride a pinned bounce buffer
-      constexpr size_t kSmall = 8192;
-      size_t small_total = 0;
-      for (size_t i = 0; i < n; i++)
-        for (uint64_t k = 0; k < items[i].niov; k++)
-          if (items[i].iov[k].len < kSmall) small_total += items[i].iov[k].len;
-      if (E->h_pack.reserve(small_total + 64)) return UNZ_ERR;
-      uint8_t* pack = static_cast<uint8_t*>(E->h_pack.p);
-      size_t   pk = 0;
+      // Host pieces.  Pieces that lie (nearly) next to each other in host memory -- the IDAT chunks of a PNG file are
+      // 12 bytes apart -- travel as ONE copy, gaps included, into a staging area that keeps the host layout; the
+      // gather kernel then joins them on the device.  Pieces that are exactly adjacent share one descriptor.
+      struct Span { const uint8_t* h; size_t len; size_t dev_off; };
+      struct Seg  { uint32_t span; size_t span_off; size_t len; size_t dst_off; };
+      std::vector<Span> spans;
+      std::vector<Seg>  segs;
+      size_t stage_total = 0;
       for (size_t i = 0; i < n; i++) {
-        size_t at = in_off[i], run_at = 0, run_pk = 0, run_len = 0;
-        auto flush = [&]() -> int {
-          if (run_len)
-            CU_TRY(cudaMemcpyAsync(din + run_at, pack + run_pk, run_len, cudaMemcpyHostToDevice, st), "H2D packed pieces");
-          run_len = 0;
-          return UNZ_OK;
-        };
+        size_t at = in_off[i];
+        bool   first = true;
         for (uint64_t k = 0; k < items[i].niov; k++) {
-          const size_t len = items[i].iov[k].len;
-          if (len < kSmall) {
-            if (!run_len) { run_at = at; run_pk = pk; }
-            std::memcpy(pack + pk, items[i].iov[k].ptr, len);
-            pk += len; run_len += len;
-          } else {
-            if (flush() != UNZ_OK) return UNZ_ERR;
-            CU_TRY(cudaMemcpyAsync(din + at, items[i].iov[k].ptr, len, cudaMemcpyHostToDevice, st), "H2D piece");
+          const uint8_t* p  = static_cast<const uint8_t*>(items[i].iov[k].ptr);
+          const size_t  len = items[i].iov[k].len;
+          if (!len) continue;
+          bool extend = false;
+          if (!spans.empty()) {
+            const uint8_t* end = spans.back().h + spans.back().len;
+            extend = p >= end && (size_t)(p - end) <= kGapMerge;
           }
+          if (extend) {
+            Span& sp = spans.back();
+            const bool glued = !first && !segs.empty() && segs.back().span == spans.size() - 1 &&
+                               sp.h + segs.back().span_off + segs.back().len == p;
+            const size_t off = (size_t)(p - sp.h);
+            sp.len = off + len;
+            if (glued) segs.back().len += len;
+            else segs.push_back({(uint32_t)(spans.size() - 1), off, len, at});
+          } else {
+            stage_total = align_up(stage_total);
+            spans.push_back({p, len, stage_total});
+            segs.push_back({(uint32_t)(spans.size() - 1), 0, len, at});
+          }
+          stage_total = spans.back().dev_off + spans.back().len;
           at += len;
+          first = false;
         }
-        if (flush() != UNZ_OK) return UNZ_ERR;
+      }
+      const size_t ns2 = segs.size();
+      if (ns2) {
+        if (E->d_stage.reserve(stage_total + 64) || E->h_seg.reserve(ns2 * 24 + 64) || E->d_seg.reserve(ns2 * 24 + 64)) return UNZ_ERR;
+        uint8_t* dstage = static_cast<uint8_t*>(E->d_stage.p);
+        for (const Span& sp : spans)
+          CU_TRY(cudaMemcpyAsync(dstage + sp.dev_off, sp.h, sp.len, cudaMemcpyHostToDevice, st), "H2D pieces");
+        auto* hs_src = static_cast<const void**>(E->h_seg.p);
+        auto* hs_len = reinterpret_cast<uint64_t*>(hs_src + ns2);
+        auto* hs_off = hs_len + ns2;
+        for (size_t k = 0; k < ns2; k++) {
+          hs_src[k] = dstage + spans[segs[k].span].dev_off + segs[k].span_off;
+          hs_len[k] = segs[k].len;
+          hs_off[k] = segs[k].dst_off;
+        }
+        CU_TRY(cudaMemcpyAsync(E->d_seg.p, E->h_seg.p, ns2 * 24, cudaMemcpyHostToDevice, st), "H2D gather table");
+        auto* ds_src = static_cast<const void* const*>(E->d_seg.p);
+        auto* ds_len = reinterpret_cast<const uint64_t*>(ds_src + ns2);
+        if (infl_gather_device(ds_src, ds_len, ds_len + ns2, ns2, din, st) != UNZ_OK) return UNZ_ERR;
       }
     }
 
@@ -1181,18 +1212,9 @@ UNZ_EXPORT int infl_buf_batch_iov(const infl_batch_iov_item_t* items, size_t n, 
       flat[i].dst = dev_ptrs ? items[i].dst : static_cast<void*>(dout + out_off[i]);
       flat[i].dstlen = items[i].dstlen;
     }
-    if (E->d_items.reserve(n * sizeof(infl_batch_item_t)) || E->d_results.reserve(n * sizeof(infl_batch_result_t)) ||
-        E->d_order.reserve(n * sizeof(uint32_t)) || E->d_ws.reserve_exact(warp_kernel_workspace(E->sms)) || E->h_order.reserve(n * sizeof(uint32_t)))
-      return UNZ_ERR;
-    auto* ho = static_cast<uint32_t*>(E->h_order.p);
-    size_order(flat.data(), n, ho);
-    CU_TRY(cudaMemcpyAsync(E->d_items.p, flat.data(), n * sizeof(flat[0]), cudaMemcpyHostToDevice, st), "H2D descriptors");
-    CU_TRY(cudaMemcpyAsync(E->d_order.p, ho, n * sizeof(*ho), cudaMemcpyHostToDevice, st), "H2D order");
-    rc = launch_batch_any(E->sms, static_cast<infl_batch_item_t*>(E->d_items.p), static_cast<uint32_t*>(E->d_order.p),
-                          n, flags, static_cast<infl_batch_result_t*>(E->d_results.p), E->d_ws.p, st);
+    // the gathered streams are an ordinary device-resident batch from here on (large members take the split decoder)
+    rc = run_device_batch_locked(E, flat.data(), n, flags, res.data());
     if (rc != UNZ_OK) return rc;
-    CU_TRY(cudaMemcpyAsync(res.data(), E->d_results.p, n * sizeof(res[0]), cudaMemcpyDeviceToHost, st), "D2H results");
-    CU_TRY(cudaStreamSynchronize(st), "inflate kernel");
     if (!dev_ptrs) {
       for (size_t i = 0; i < n; i++)
         if (res[i].outlen)
