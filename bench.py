@@ -598,7 +598,7 @@ def main():
             tj = json.load(open(prof))
             roofline["traffic"] = float(tj["dram_bytes_over_algorithmic_bytes"]) * (in_bytes + out_bytes)
             roofline["traffic_source"] = "ncu dram bytes / algorithmic bytes = %.2f at 16000 streams per launch (%s), scaled to this launch" % (
-                tj["dram_bytes_over_algorithmic_bytes"], "profiles/r01_v3c_ncu_full_summary.json")
+                tj["dram_bytes_over_algorithmic_bytes"], "profiles/r01_v3d_ncu_full_summary.json")
         except Exception:
             pass
 
