@@ -71,4 +71,22 @@ DEFL_DEV uint32_t reduce_max(unsigned mask, uint32_t v) { return __reduce_max_sy
 // tokens written to the global scratch by one lane and read back by the whole warp: L2 only
 DEFL_DEV uint32_t ld_tok(const uint32_t* p) { return __ldcg(p); }
 
+// global -> shared without a register in between (LDGSTS): the copy is in flight while the lane decodes on, and
+// nothing waits for it until cp_async_wait<N>() ("all but my N newest groups have landed").  valid = false zero-fills.
+DEFL_DEV void cp_async4(void* smem_dst, const void* gsrc, bool valid) {
+  const unsigned s = (unsigned)__cvta_generic_to_shared(smem_dst);
+  const size_t   g = __cvta_generic_to_global(gsrc);
+  const int      n = valid ? 4 : 0;
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(s), "l"(g), "r"(n) : "memory");
+}
+DEFL_DEV void cp_async16(void* smem_dst, const void* gsrc, bool valid) {      // both 16-byte aligned
+  const unsigned s = (unsigned)__cvta_generic_to_shared(smem_dst);
+  const size_t   g = __cvta_generic_to_global(gsrc);
+  const int      n = valid ? 16 : 0;
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(s), "l"(g), "r"(n) : "memory");
+}
+DEFL_DEV void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+DEFL_DEV void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
 }  // namespace simt

@@ -90,12 +90,56 @@ struct SubReader {
   }
 };
 
+// The reader of the speculative pass.  Same window as SubReader, but the words ahead travel global -> shared by
+// cp.async, 16 bytes at a time, into two slots per lane (ring[slot * 128 + lane * 4 + word]) instead of one word at a
+// time into a register: a quarter of the load instructions and of the L2 sectors touched (the lanes of an SM stream
+// through more lines than its L1 holds, so a 4-byte load mostly paid for a whole sector), and nothing waits for a
+// quad until four to eight words after it was requested.  drain() before the shared memory is used for anything else.
+struct RingReader {
+  const uint32_t* w;
+  uint32_t        wend, widx;
+  uint32_t        w0, w1, w2;
+  uint32_t        bo;
+  uint32_t*       ring;            // this lane's 4 words of slot 0
+  uint32_t        skew;            // words between w and the 16-byte boundary below it (0..3)
+  const uint8_t*  quads;           // that boundary
+
+  // quad q holds words 4q - skew .. 4q - skew + 3 of the stream
+  DEFL_DEV void request(uint32_t q) {
+    const bool in = 4u * q < wend + skew;               // its first word may lie before w: same 16 bytes, never read
+    simt::cp_async16(ring + (q & 1u) * 128u, quads + (in ? (size_t)q * 16u : 0u), in);
+    simt::cp_async_commit();
+  }
+  DEFL_DEV void from(const SubReader& s, uint32_t* ring_lane) {
+    w = s.w; wend = s.wend; widx = s.widx; w0 = s.w0; w1 = s.w1; w2 = s.w2; bo = s.bo; ring = ring_lane;
+    skew  = (uint32_t)(((uintptr_t)w >> 2) & 3u);
+    quads = reinterpret_cast<const uint8_t*>((uintptr_t)w & ~(uintptr_t)15);
+    const uint32_t q = (widx + 3u + skew) >> 2;          // the quad of the next word the window needs
+    request(q); request(q + 1u);
+  }
+  DEFL_DEV void consume(uint32_t n) {     // n <= 48, bo < 32 on entry
+    bo += n;
+#pragma unroll 1
+    while (bo >= 32u) {
+      const uint32_t i = widx + 3u;                      // the word that enters the window
+      const uint32_t a = i + skew, q = a >> 2, k = a & 3u;
+      simt::cp_async_wait<1>();                          // quad q has landed (q + 1 may still be on its way)
+      const uint32_t v = ring[(q & 1u) * 128u + k];
+      w0 = w1; w1 = w2; w2 = i < wend ? v : 0u;
+      if (k == 3u) request(q + 2u);                      // its slot is free now
+      widx++; bo -= 32u;
+    }
+  }
+  DEFL_DEV void drain() { simt::cp_async_wait<0>(); }
+};
+
 DEFL_DEV uint32_t fail_stat(uint32_t reason) { return LS_FAIL | (reason << 8); }
 
 // Decode the token that starts at the reader's position.  `avail` = input bits from here to the end
 // of the stream; a symbol whose bits are not all there fails (infl.c:741-745,806-810).
 // Returns LS_OK with (tok, used), LS_EOB with used = the code's bits, or LS_FAIL | reason << 8.
-DEFL_DEV uint32_t decode_token(const uint16_t* lit, const uint16_t* dist, const SubReader& br, uint32_t avail,
+template <typename READER>
+DEFL_DEV uint32_t decode_token(const uint16_t* lit, const uint16_t* dist, const READER& br, uint32_t avail,
                                bool pack, uint32_t& tok, uint32_t& used) {
   const uint32_t v0 = simt::funnel_r(br.w0, br.w1, br.bo);
   const uint32_t v1 = simt::funnel_r(br.w1, br.w2, br.bo);
@@ -155,7 +199,7 @@ struct LaneTraj {
 // running pointers for the token and checkpoint stores.
 DEFL_DEV void lane_spec(const uint16_t* lit, const uint16_t* dist, const uint32_t* words, uint32_t wend,
                         uint32_t bw, uint32_t start, uint32_t limit, uint32_t endr, uint32_t* seg,
-                        uint16_t* cps, LaneTraj& tj, uint32_t warm) {
+                        uint16_t* cps, LaneTraj& tj, uint32_t warm, uint32_t* ring_lane) {
   SubReader br;
   br.w = words; br.wend = wend;
   uint32_t r = start;
@@ -179,6 +223,8 @@ DEFL_DEV void lane_spec(const uint16_t* lit, const uint16_t* dist, const uint32_
     br.seek(bw, start);
   }
   const uint32_t  r0 = r;
+  RingReader rr;
+  rr.from(br, ring_lane);
   uint32_t        next_cp = start, stat = LS_OK;
   uint32_t*       tp = seg;
   uint32_t* const tend = seg + kSpecCap;
@@ -188,8 +234,8 @@ DEFL_DEV void lane_spec(const uint16_t* lit, const uint16_t* dist, const uint32_
   for (;;) {
     // ---- fast loop
     while (r < fast_limit && tp != tend) {
-      const uint32_t v0 = simt::funnel_r(br.w0, br.w1, br.bo);
-      const uint32_t v1 = simt::funnel_r(br.w1, br.w2, br.bo);
+      const uint32_t v0 = simt::funnel_r(rr.w0, rr.w1, rr.bo);
+      const uint32_t v1 = simt::funnel_r(rr.w1, rr.w2, rr.bo);
       uint32_t       e  = lit[v0 & (kLitRoot - 1)];
       if ((e & (kLitIsLen | kLitKind)) == kLitSub)
         e = lit[kLitRoot + (e & 0x1FFu) + ((v0 >> kLitRootBits) & ((1u << ((e >> 11) & 15u)) - 1u))];
@@ -217,7 +263,7 @@ DEFL_DEV void lane_spec(const uint16_t* lit, const uint16_t* dist, const uint32_
       }
       *tp++ = tok;
       r += used;
-      br.consume(used);
+      rr.consume(used);
     }
     // ---- one careful step: the ends of the sub-sequence, the input and the block, failures
     if (r >= limit) break;
@@ -227,7 +273,7 @@ DEFL_DEV void lane_spec(const uint16_t* lit, const uint16_t* dist, const uint32_
       next_cp += kCpBits;
     }
     uint32_t tok, used;
-    const uint32_t s = decode_token(lit, dist, br, endr > r ? endr - r : 0u, true, tok, used);
+    const uint32_t s = decode_token(lit, dist, rr, endr > r ? endr - r : 0u, true, tok, used);
     if (s != LS_OK) {
       stat = s;
       if (s == LS_EOB) r += used;
@@ -235,8 +281,9 @@ DEFL_DEV void lane_spec(const uint16_t* lit, const uint16_t* dist, const uint32_
     }
     *tp++ = tok;
     r += used;
-    br.consume(used);
+    rr.consume(used);
   }
+  rr.drain();
   const uint32_t t = (uint32_t)(tp - seg);
   tj.land = r; tj.stat = stat; tj.n = t; tj.m = 0; tj.nf = 0; tj.T = r0; tj.ncp = (uint32_t)(cpp - cps);
   tj.s_land = r; tj.s_stat = stat; tj.s_n = t;
@@ -546,7 +593,9 @@ DEFL_DEV uint32_t decode_window(WarpSmem& sm, const WarpScratch& sc, int lane, c
   tj.land = start; tj.stat = LS_NONE; tj.n = 0; tj.m = 0; tj.nf = 0; tj.T = start; tj.ncp = 0;
   tj.s_land = start; tj.s_stat = LS_NONE; tj.s_n = 0;
   const uint32_t warm = (lane >= 1 && active) ? (warm_bits < S ? warm_bits : S) : 0u;      // lane 0 starts on a known boundary
-  if (active) lane_spec(sm.lit, sm.dist, words, wend, bw, start, limit, endr, seg, cps, tj, warm);
+  // the resolver's stage is idle during the speculative pass: it holds the lanes' input rings
+  if (active) lane_spec(sm.lit, sm.dist, words, wend, bw, start, limit, endr, seg, cps, tj, warm,
+                        reinterpret_cast<uint32_t*>(sm.stage) + lane * 4);
   simt::syncwarp(kFull);
 
   // fix-up rounds until every lane starts where its predecessor ended

@@ -139,4 +139,13 @@ inline uint32_t reduce_max(unsigned, uint32_t v) {
 }
 inline uint32_t ld_tok(const uint32_t* p) { return *(const volatile uint32_t*)p; }
 
+inline void cp_async4(void* smem_dst, const void* gsrc, bool valid) {
+  if (valid) memcpy(smem_dst, gsrc, 4); else memset(smem_dst, 0, 4);
+}
+inline void cp_async16(void* smem_dst, const void* gsrc, bool valid) {
+  if (valid) memcpy(smem_dst, gsrc, 16); else memset(smem_dst, 0, 16);
+}
+inline void cp_async_commit() {}
+template <int N> inline void cp_async_wait() {}
+
 }  // namespace simt
