@@ -451,3 +451,26 @@ def test_split_paths_on_damaged_streams(gpu_lib):
         if code == 0:
             assert int(g["outlen"]) == len(want) and int(g["adler"]) == r.adler, i
             assert t[: len(want)].cpu().numpy().tobytes() == want, i
+
+
+@pytest.mark.gpu
+def test_all_gpus_in_one_process(gpu_lib):
+    """INFL_BATCH_ALL_GPUS: one host batch sharded over every visible device inside one process (byte-balanced, one
+    host thread and one copy/compute pipeline per device, no exchange).  With one GPU it is the same path with one
+    shard.  Results equal the oracle's and do not depend on how many devices took part."""
+    import torch
+    from defl_b200 import synth
+    d = gpu_lib
+    specs = synth.config5_specs(24 << 20, first_seed=4242, lo=4096, hi=1 << 20)
+    streams = synth.make_streams(specs, threads=4)
+    zs = [z for _, z in streams]
+    caps = [len(r) for r, _ in streams]
+    flags = d.INFL_ZLIB | d.INFL_BATCH_VERIFY_ADLER
+    res1, outs1 = d.infl_buf_batch(zs, caps, flags)
+    resn, outsn = d.infl_buf_batch(zs, caps, flags | d.INFL_BATCH_ALL_GPUS)
+    for (raw, z), a, b, oa, ob in zip(streams, res1, resn, outs1, outsn):
+        assert int(a["code"]) == 0 and int(b["code"]) == 0
+        assert bytes(oa) == raw and bytes(ob) == raw
+        for f in ("adler", "outlen", "inpos", "adler_stored"):
+            assert int(a[f]) == int(b[f]), f
+    assert torch.cuda.device_count() >= 1
