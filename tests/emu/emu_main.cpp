@@ -205,6 +205,7 @@ struct ChunkJob {
   defl::SplitChunkOut* out;
   uint32_t*           tok;      // count: where tokens are kept; decode: tokens to replay (with ntok)
   uint32_t            tokcap, ntok;
+  uint32_t            mode, start_final;
 };
 
 void* chunk_main(void* arg) {
@@ -217,10 +218,12 @@ void* chunk_main(void* arg) {
     defl::TokSink sink;
     sink.buf = j->tok; sink.cap = j->tokcap; sink.n = 0; sink.ok = j->tok != nullptr;
     defl::inflate_chunk_warp<uint16_t, true>(*j->sm, defl::scratch_of(j->scratch), j->lane, j->src, j->srclen, j->cand,
-                                             j->ncand, j->me, nullptr, 0xFFFFFFFFu, hist, o, &sink);
+                                             j->ncand, j->me, nullptr, 0xFFFFFFFFu, hist, o, &sink, nullptr, defl::kNoTokens,
+                                             j->mode, j->start_final);
   } else {
     defl::inflate_chunk_warp<uint16_t, false>(*j->sm, defl::scratch_of(j->scratch), j->lane, j->src, j->srclen, j->cand,
-                                              j->ncand, j->me, j->dst, j->cap, hist, o, nullptr, j->tok, j->ntok);
+                                              j->ncand, j->me, j->dst, j->cap, hist, o, nullptr, j->tok, j->ntok, j->mode,
+                                              j->start_final);
   }
   if (j->lane == 0) *j->out = o;
   return nullptr;
@@ -228,13 +231,14 @@ void* chunk_main(void* arg) {
 
 void run_chunk(defl::WarpSmem* sm, void* scratch, const uint8_t* src, uint32_t srclen, const uint64_t* cand,
                uint32_t ncand, uint32_t me, uint16_t* dst, uint32_t cap, bool count, defl::SplitChunkOut* out,
-               uint32_t* tok = nullptr, uint32_t tokcap = 0, uint32_t ntok = defl::kNoTokens) {
+               uint32_t* tok = nullptr, uint32_t tokcap = 0, uint32_t ntok = defl::kNoTokens,
+               uint32_t mode = defl::MODE_BLOCK_STARTS, uint32_t start_final = defl::FIN_UNKNOWN) {
   simt::Group grp;
   grp.G = 32;
   pthread_barrier_init(&grp.bar, nullptr, 32);
   std::vector<ChunkJob>  jobs(32);
   std::vector<pthread_t> th(32);
-  for (int i = 0; i < 32; i++) jobs[i] = ChunkJob{&grp, i, sm, scratch, src, srclen, cand, ncand, me, dst, cap, count, out, tok, tokcap, ntok};
+  for (int i = 0; i < 32; i++) jobs[i] = ChunkJob{&grp, i, sm, scratch, src, srclen, cand, ncand, me, dst, cap, count, out, tok, tokcap, ntok, mode, start_final};
   for (int i = 1; i < 32; i++) pthread_create(&th[i], nullptr, chunk_main, &jobs[i]);
   chunk_main(&jobs[0]);
   for (int i = 1; i < 32; i++) pthread_join(th[i], nullptr);
@@ -289,6 +293,127 @@ extern "C" long emu_split_inflate(const uint8_t* src, uint32_t srclen, const uin
       for (uint64_t i = 0; i < total; i++) {
         while (cc + 1 < chain.size() && off[cc + 1] <= i) cc++;
         dst[i] = (uint8_t)defl::resolve_marker(sym.data(), off.data(), cc, i);
+      }
+      rc = (long)total;
+    }
+  }
+  free(sm); free(scratch);
+  return rc;
+}
+
+// ---- split decode of a fixed-Huffman stream from token boundaries inside its blocks (MODE_FIXED_MID) ----
+namespace {
+struct ProbeJob {
+  simt::Group*    grp;
+  int             lane;
+  defl::WarpSmem* sm;
+  const uint8_t*  src;
+  uint32_t        srclen, body, granule, probe_bits, ngran;
+  uint64_t*       found;
+};
+
+void* probe_main(void* arg) {
+  ProbeJob* j = static_cast<ProbeJob*>(arg);
+  simt::t_group = j->grp;
+  simt::t_lane  = j->lane;
+  defl::Lane<32> L;
+  L.gmask = defl::kFull; L.lane = j->lane; L.wlane = j->lane;
+  defl::BitReader none;
+  none.w = nullptr; none.wend = 0;
+  bool fixed_ready = false;
+  defl::huffman_block_setup<32>(L, j->sm->lit, j->sm->dist, j->sm->s, none, 0, 1u, fixed_ready);
+  simt::syncwarp(defl::kFull);
+  const uint32_t  mis      = (uint32_t)((uintptr_t)j->src & 3u);
+  const uint64_t  base_bit = (uint64_t)mis * 8u;
+  const uint64_t  end_bit  = base_bit + (uint64_t)j->srclen * 8u;
+  const uint32_t* words    = reinterpret_cast<const uint32_t*>((uintptr_t)j->src - mis);
+  const uint32_t  wend     = (uint32_t)(((uint64_t)mis + j->srclen + 3u) >> 2);
+  for (uint32_t g = 1 + (uint32_t)j->lane; g < j->ngran; g += 32) {
+    const uint64_t p = base_bit + ((uint64_t)j->body + (uint64_t)g * j->granule) * 8u;
+    const uint64_t r = defl::fixed_probe_lane(j->sm->lit, j->sm->dist, words, wend, p, end_bit, j->probe_bits);
+    j->found[g] = r == defl::kNoCandidate ? r : r - base_bit;
+  }
+  return nullptr;
+}
+}  // namespace
+
+// src: a stream whose blocks are all fixed-Huffman, body at byte `body`.  The host side of split_decode_many's
+// mid-block mode restated for one stream: probe, count, chain walk carrying block finality, decode, resolve.
+// ncand_out: candidates used; nchain_out: chunks on the true chain.
+extern "C" long emu_split_inflate_mid(const uint8_t* src, uint32_t srclen, uint32_t body, uint32_t granule,
+                                      uint32_t probe_bits, uint8_t* dst, uint32_t cap, uint64_t* end_bit,
+                                      uint32_t* ncand_out, uint32_t* nchain_out) {
+  using namespace defl;
+  WarpSmem* sm = static_cast<WarpSmem*>(aligned_alloc(64, (sizeof(WarpSmem) + 63) & ~63ul));
+  void* scratch = aligned_alloc(64, kWarpScratchBytes);
+  const uint32_t ngran = (srclen - body + granule - 1) / granule;
+  std::vector<uint64_t> found(ngran, kNoCandidate);
+  {
+    simt::Group grp;
+    grp.G = 32;
+    pthread_barrier_init(&grp.bar, nullptr, 32);
+    std::vector<ProbeJob>  jobs(32);
+    std::vector<pthread_t> th(32);
+    for (int i = 0; i < 32; i++) jobs[i] = ProbeJob{&grp, i, sm, src, srclen, body, granule, probe_bits, ngran, found.data()};
+    for (int i = 1; i < 32; i++) pthread_create(&th[i], nullptr, probe_main, &jobs[i]);
+    probe_main(&jobs[0]);
+    for (int i = 1; i < 32; i++) pthread_join(th[i], nullptr);
+    pthread_barrier_destroy(&grp.bar);
+  }
+  std::vector<uint64_t> cand{(uint64_t)body * 8u};
+  for (uint32_t g = 1; g < ngran; g++)
+    if (found[g] != kNoCandidate && found[g] > cand.back()) cand.push_back(found[g]);
+  const uint32_t ncand = (uint32_t)cand.size();
+  *ncand_out = ncand;
+
+  std::vector<SplitChunkOut> outs(ncand);
+  std::vector<std::vector<uint32_t>> toks(ncand);
+  for (uint32_t i = 0; i < ncand; i++) {
+    const uint64_t b0 = cand[i] >> 3, b1 = i + 1 < ncand ? cand[i + 1] >> 3 : srclen;
+    toks[i].resize(3 * (b1 - b0) + 1);
+    run_chunk(sm, scratch, src, srclen, cand.data(), ncand, i, nullptr, 0, true, &outs[i], toks[i].data(),
+              (uint32_t)toks[i].size() - 1, kNoTokens, MODE_FIXED_MID, FIN_UNKNOWN);
+  }
+  struct Item { uint32_t cand, bytes, ntok, start_final; };
+  std::vector<Item>     chain;
+  std::vector<uint64_t> off;
+  uint64_t total = 0;
+  long     rc = 0;
+  uint32_t fin = FIN_NO;
+  for (uint32_t k = 0;;) {
+    const SplitChunkOut& o = outs[k];
+    if ((o.status & 0xFF) == CH_FAIL && !(fin == FIN_YES && o.has_eob)) { rc = -1; break; }
+    const bool ends_here = fin == FIN_YES && k != 0 && o.has_eob;
+    if (fin == FIN_YES && k != 0 && !o.has_eob && o.status != CH_LINKED) { rc = -5; break; }
+    const uint32_t bytes = ends_here ? o.eob_bytes : o.out_bytes;
+    chain.push_back({k, bytes, ends_here ? o.eob_ntok : o.ntok, k == 0 ? (uint32_t)FIN_NO : fin});
+    off.push_back(total);
+    total += bytes;
+    if (total > cap) { rc = -2; break; }
+    if (ends_here) { *end_bit = o.eob_bit; break; }
+    if (o.status == CH_FINAL) { *end_bit = o.end_bit; break; }
+    if (o.status != CH_LINKED || o.link <= k || o.link >= ncand) { rc = -3; break; }
+    if (o.link_final != FIN_UNKNOWN) fin = o.link_final;
+    k = o.link;
+  }
+  *nchain_out = (uint32_t)chain.size();
+  if (rc == 0) {
+    off.push_back(total);
+    std::vector<uint16_t> sym(total + 8, 0xFFFF);
+    for (size_t k = 0; k < chain.size() && rc == 0; k++) {
+      SplitChunkOut o2;
+      const bool replay = (k & 1) && chain[k].ntok != kNoTokens;
+      run_chunk(sm, scratch, src, srclen, cand.data(), ncand, chain[k].cand, sym.data() + off[k], chain[k].bytes, false, &o2,
+                toks[chain[k].cand].data(), 0, replay ? chain[k].ntok : kNoTokens, MODE_FIXED_MID, chain[k].start_final);
+      if (replay ? (o2.status != CH_REPLAYED || o2.out_bytes != chain[k].bytes)
+                 : ((o2.status & 0xFF) == CH_FAIL || o2.out_bytes != chain[k].bytes)) rc = -4 - 10 * (long)k;
+      if (replay) g_replayed++;
+    }
+    if (rc == 0) {
+      uint32_t cc = 0;
+      for (uint64_t i = 0; i < total; i++) {
+        while (cc + 1 < chain.size() && off[cc + 1] <= i) cc++;
+        dst[i] = (uint8_t)resolve_marker(sym.data(), off.data(), cc, i);
       }
       rc = (long)total;
     }

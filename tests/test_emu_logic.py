@@ -27,7 +27,8 @@ class StreamOut(ctypes.Structure):
 @pytest.fixture(scope="module")
 def emu():
     srcs = [os.path.join(EMU_DIR, "emu_main.cpp"), os.path.join(EMU_DIR, "simt_emu.h"), CORE,
-            os.path.join(CSRC, "pipeline.cuh"), os.path.join(CSRC, "warp_decode.cuh")]
+            os.path.join(CSRC, "pipeline.cuh"), os.path.join(CSRC, "warp_decode.cuh"),
+            os.path.join(CSRC, "split_decode.cuh")]
     if not os.path.exists(EMU_SO) or any(os.path.getmtime(s) > os.path.getmtime(EMU_SO) for s in srcs):
         subprocess.check_call(["g++", "-std=c++17", "-O1", "-fPIC", "-shared", "-pthread", "-w",
                                "-o", EMU_SO, srcs[0]])
@@ -189,3 +190,32 @@ def test_split_chunks_and_markers_logic(emu):
         assert (end_bit.value + 7) // 8 == len(z) - 4
     emu.emu_split_replayed.restype = ctypes.c_long
     assert emu.emu_split_replayed() > 0      # some chunks took the kept-token replay path
+
+
+def test_split_mid_block_fixed_logic(emu):
+    """Fixed-Huffman streams (zlib's Z_FIXED: one block, or a few) have no block starts to split at: chunks start
+    at token boundaries found by the probe, link where a chunk's trajectory meets a later candidate, and the chain
+    walk carries whether the block they start in is the stream's last.  Bytes equal the oracle's."""
+    from defl_b200 import synth
+    emu.emu_split_inflate_mid.restype = ctypes.c_long
+    before = emu.emu_split_replayed()
+    for kind, size, granule, probe in (("text", 260000, 16384, 16384), ("log", 200000, 8192, 4096),
+                                       ("png", 150000, 16384, 16384)):
+        raw, z = synth.make_streams([(kind, size, 33, 6, zlib.Z_FIXED)], threads=1)[0]
+        rc0, out0, r0 = ol.port_inflate(z, len(raw), 1)
+        assert rc0 == 0 and out0 == raw
+        buf = ctypes.create_string_buffer(len(z) + 16)
+        base = ctypes.addressof(buf)
+        off = (-base) % 4 + 1
+        ctypes.memmove(base + off, z, len(z))
+        dst = ctypes.create_string_buffer(len(raw) + 16)
+        end_bit = ctypes.c_uint64(0)
+        ncand = ctypes.c_uint32(0)
+        nchain = ctypes.c_uint32(0)
+        n = emu.emu_split_inflate_mid(ctypes.c_void_p(base + off), len(z), 2, granule, probe, dst, len(raw),
+                                      ctypes.byref(end_bit), ctypes.byref(ncand), ctypes.byref(nchain))
+        assert n == len(raw), (kind, n, ncand.value, nchain.value)
+        assert dst.raw[:n] == raw, kind
+        assert (end_bit.value + 7) // 8 == len(z) - 4
+        assert ncand.value >= 4 and nchain.value >= ncand.value // 2, (kind, ncand.value, nchain.value)
+    assert emu.emu_split_replayed() > before
