@@ -18,6 +18,7 @@
 #include <numeric>
 #include <string>
 #include <thread>
+#include <functional>
 #include <vector>
 
 #include "../../include/defl/infl.h"
@@ -94,8 +95,10 @@ struct Engine {
   int          dev      = -1;
   int          sms      = 0;
   cudaStream_t stream   = nullptr;
+  cudaStream_t stream2  = nullptr;   // the one-warp kernel of a batch that also has split-decoded members
   std::mutex   mu;
   DevBuf       d_in, d_out, d_items, d_results, d_order, d_ws, d_seg, d_stage;
+  DevBuf       d_items2, d_results2, d_order2, d_ws2;
   PinBuf       h_items, h_results, h_order, h_pack, h_seg;
   bool         ready = false;
 };
@@ -118,6 +121,7 @@ int engine_for_current_device(Engine** out) {
       e.dev = dev;
       e.sms = prop.multiProcessorCount;
       CU_TRY(cudaStreamCreateWithFlags(&e.stream, cudaStreamNonBlocking), "cudaStreamCreate");
+      CU_TRY(cudaStreamCreateWithFlags(&e.stream2, cudaStreamNonBlocking), "cudaStreamCreate");
       e.ready = true;
     }
   }
@@ -294,8 +298,12 @@ struct SplitInput {          // one stream handed to the split decoder: device p
 // status[i] = UNZ_OK with res[i] filled when stream i was decoded here, UNZ_NOOP when it has to go through
 // the one-warp decoder instead (too few block starts, any failure: that path defines error behaviour).
 // Returns UNZ_ERR only when the engine itself failed.  d_ws is the token scratch of the batch engine.
+// after_peek (optional) is called once, with one flag per stream, as soon as the cheap stages (a look at each
+// stream's first bytes, the search for split points) have ruled some out: the caller can start those elsewhere
+// at once.
 int split_decode_many(Engine* E, const SplitInput* in, size_t nin, int flags, void* d_ws, cudaStream_t st,
-                      infl_batch_result_t* res, int* status) {
+                      infl_batch_result_t* res, int* status,
+                      const std::function<int(const std::vector<char>&)>* after_peek = nullptr) {
   using namespace defl;
   SplitBufs& SB = g_split[E->dev];
   const bool zlib = (flags & 0xFF) == INFL_ZLIB;
@@ -373,7 +381,8 @@ int split_decode_many(Engine* E, const SplitInput* in, size_t nin, int flags, vo
     ngran_total += sd[i].ngran;
   }
   if (!ngran_total) return UNZ_OK;
-  if (SB.d_found.reserve((size_t)ngran_total * 8) || upload_streams() != UNZ_OK) return UNZ_ERR;
+  // F's answers in the first ngran_total entries of d_found, P's (streams in mid-block mode) in the second
+  if (SB.d_found.reserve((size_t)ngran_total * 16) || upload_streams() != UNZ_OK) return UNZ_ERR;
   find_block_starts_kernel<kWarpsPerCta><<<(ngran_total + kWarpsPerCta - 1) / kWarpsPerCta, kWarpsPerCta * 32, 0, st>>>(
       d_sd, ns, ngran_total, granule, static_cast<uint64_t*>(SB.d_found.p));
   CU_TRY(cudaGetLastError(), "find_block_starts_kernel launch");
@@ -383,26 +392,33 @@ int split_decode_many(Engine* E, const SplitInput* in, size_t nin, int flags, vo
   if (any_fixed) {
     const unsigned per_cta = kWarpsPerCta * 32;
     fixed_probe_kernel<kWarpsPerCta><<<(ngran_total + per_cta - 1) / per_cta, per_cta, sizeof(WarpSmem) * kWarpsPerCta, st>>>(
-        d_sd, ns, ngran_total, granule, probe_bits, static_cast<uint64_t*>(SB.d_found.p));
+        d_sd, ns, ngran_total, granule, probe_bits, static_cast<uint64_t*>(SB.d_found.p) + ngran_total);
     CU_TRY(cudaGetLastError(), "fixed_probe_kernel launch");
     g_launches.fetch_add(1, std::memory_order_relaxed);
   }
-  std::vector<uint64_t> found(ngran_total);
-  CU_TRY(cudaMemcpyAsync(found.data(), SB.d_found.p, (size_t)ngran_total * 8, cudaMemcpyDeviceToHost, st), "D2H block starts");
+  std::vector<uint64_t> found((size_t)ngran_total * 2, kNoCandidate);
+  CU_TRY(cudaMemcpyAsync(found.data(), SB.d_found.p, (size_t)ngran_total * (any_fixed ? 16 : 8), cudaMemcpyDeviceToHost, st), "D2H block starts");
   CU_TRY(cudaStreamSynchronize(st), "find_block_starts_kernel");
   mark("F find_block_starts");
   std::vector<uint64_t> cand;
   for (uint32_t i = 0; i < ns; i++) {
     sd[i].cand_base = (uint32_t)cand.size();
     if (!alive[i]) continue;
+    const uint64_t* fnd = found.data() + (sd[i].mode == MODE_FIXED_MID ? ngran_total : 0u) + sd[i].gran_base;
     cand.push_back((uint64_t)sd[i].body * 8);
     for (uint32_t g = 0; g < sd[i].ngran; g++) {
-      const uint64_t f = found[sd[i].gran_base + g];
+      const uint64_t f = fnd[g];
       if (f != kNoCandidate && f >= cand.back() + min_gap && f > cand.back()) cand.push_back(f);
     }
     sd[i].ncand = (uint32_t)cand.size() - sd[i].cand_base;
-    if (sd[i].ncand < 4) { alive[i] = 0; cand.resize(sd[i].cand_base); sd[i].ncand = 0; }
+    if (sd[i].ncand < 4) {
+      if (trace) std::fprintf(stderr, "[split] given back: stream %u (%llu -> %llu bytes, mode %u) has %u candidates in %u granules\n", i,
+                              (unsigned long long)in[i].srclen, (unsigned long long)in[i].dstlen, sd[i].mode, sd[i].ncand, sd[i].ngran);
+      alive[i] = 0; cand.resize(sd[i].cand_base); sd[i].ncand = 0;
+    }
   }
+  // from here on only a broken chain (damaged input, a false block start that decodes) sends a stream back
+  if (after_peek && (*after_peek)(alive) != UNZ_OK) return UNZ_ERR;
   const uint32_t ncand = (uint32_t)cand.size();
   if (!ncand) return UNZ_OK;
 
@@ -524,7 +540,11 @@ int split_decode_many(Engine* E, const SplitInput* in, size_t nin, int flags, vo
     }
     // markers index the 32 KiB before a chunk: they must exist
     if (ok && chain.size() - chain0 > 1 && off[off0 + 1] < kWinBytes) ok = false;
-    if (!ok) { alive[i] = 0; chain.resize(chain0); off.resize(off0); continue; }
+    if (!ok) {
+      if (trace) std::fprintf(stderr, "[split] given back: stream %u (%llu -> %llu bytes, mode %u): chain of %zu chunks broke after %llu bytes\n", i,
+                              (unsigned long long)in[i].srclen, (unsigned long long)in[i].dstlen, sd[i].mode, chain.size() - chain0, (unsigned long long)total);
+      alive[i] = 0; chain.resize(chain0); off.resize(off0); continue;
+    }
     off.push_back(total);
     sd[i].nchunk = (uint32_t)(chain.size() - chain0);
     sd[i].total  = total;
@@ -665,7 +685,7 @@ bool wants_split(const infl_batch_item_t& it, uint64_t batch_bytes, uint64_t res
   if (it.srclen >= kSplitMinBytes) return true;
   if (it.srclen < kSplitMinInBatch) return false;
   // DEFL_SPLIT_TAIL_PCT: a stream is split when its share of the batch exceeds this percentage of 1 / resident warps
-  static const uint32_t pct = env_u32("DEFL_SPLIT_TAIL_PCT", 25u, 1u, 100000u);
+  static const uint32_t pct = env_u32("DEFL_SPLIT_TAIL_PCT", 60u, 1u, 100000u);
   return (it.srclen + it.dstlen) * resident_warps * 100u > batch_bytes * pct;
 }
 
@@ -896,29 +916,71 @@ int run_device_batch_locked(Engine* E, const infl_batch_item_t* items, size_t n,
         rest.push_back(items[i]); rest_idx.push_back(i);
       }
     }
+    // The members that stay on one warp start first, on their own stream and scratch: the batch kernel is
+    // persistent, so the split kernels (queued behind it) take over the SMs as its CTAs run out of streams, and
+    // the long tail of its largest members is hidden behind them.
+    const bool trace = std::getenv("DEFL_SPLIT_TRACE") != nullptr;
+    const auto t_begin = std::chrono::steady_clock::now();
+    std::vector<uint32_t> ord;
+    std::vector<char>     early(sin.size(), 0);      // given back right after the peek: they join the one-warp launch
+    bool launched = false;
+    auto launch_rest = [&](const std::vector<char>& alive) -> int {
+      launched = true;
+      for (size_t k = 0; k < alive.size() && k < sin.size(); k++)
+        if (!alive[k]) { early[k] = 1; rest.push_back(items[sin_idx[k]]); rest_idx.push_back(sin_idx[k]); }
+      if (rest.empty()) return UNZ_OK;
+      ord.resize(rest.size());
+      if (E->d_items2.reserve(rest.size() * sizeof(infl_batch_item_t)) || E->d_results2.reserve(rest.size() * sizeof(infl_batch_result_t)) ||
+          E->d_order2.reserve(rest.size() * sizeof(uint32_t)) || E->d_ws2.reserve_exact(warp_kernel_workspace(E->sms)))
+        return UNZ_ERR;
+      size_order(rest.data(), rest.size(), ord.data());
+      CU_TRY(cudaMemcpyAsync(E->d_items2.p, rest.data(), rest.size() * sizeof(rest[0]), cudaMemcpyHostToDevice, E->stream2), "H2D descriptors");
+      CU_TRY(cudaMemcpyAsync(E->d_order2.p, ord.data(), rest.size() * sizeof(ord[0]), cudaMemcpyHostToDevice, E->stream2), "H2D order");
+      return launch_batch_any(E->sms, static_cast<infl_batch_item_t*>(E->d_items2.p), static_cast<uint32_t*>(E->d_order2.p),
+                              rest.size(), flags, static_cast<infl_batch_result_t*>(E->d_results2.p), E->d_ws2.p, E->stream2);
+    };
+    const std::function<int(const std::vector<char>&)> hook = launch_rest;
     std::vector<infl_batch_result_t> sres(sin.size());
     std::vector<int>                 sstat(sin.size(), UNZ_NOOP);
-    if (split_decode_many(E, sin.data(), sin.size(), flags, E->d_ws.p, st, sres.data(), sstat.data()) != UNZ_OK) return UNZ_ERR;
+    int src = split_decode_many(E, sin.data(), sin.size(), flags, E->d_ws.p, st, sres.data(), sstat.data(), &hook);
+    if (!launched && src == UNZ_OK) src = launch_rest(std::vector<char>(sin.size(), 1));   // the split path left before its peek
+    const auto t_split = std::chrono::steady_clock::now();
+    if (!rest.empty()) {
+      std::vector<infl_batch_result_t> rr(rest.size());
+      CU_TRY(cudaMemcpyAsync(rr.data(), E->d_results2.p, rr.size() * sizeof(rr[0]), cudaMemcpyDeviceToHost, E->stream2), "D2H results");
+      CU_TRY(cudaStreamSynchronize(E->stream2), "inflate kernel");
+      for (size_t k = 0; k < rr.size(); k++) results[rest_idx[k]] = rr[k];
+    }
+    if (src != UNZ_OK) return UNZ_ERR;
+    const auto t_rest = std::chrono::steady_clock::now();
+    // members the split path gave back (no usable split points, or damaged): one warp each, as if never tried
+    std::vector<infl_batch_item_t> back;
+    std::vector<size_t>            back_idx;
     for (size_t k = 0; k < sin.size(); k++) {
       if (sstat[k] == UNZ_OK) results[sin_idx[k]] = sres[k];
-      else { rest.push_back(items[sin_idx[k]]); rest_idx.push_back(sin_idx[k]); }
+      else if (!early[k]) { back.push_back(items[sin_idx[k]]); back_idx.push_back(sin_idx[k]); }
     }
-    if (rest.empty()) return UNZ_OK;
-    std::vector<infl_batch_result_t> rr(rest.size());
-    auto* ho2 = static_cast<uint32_t*>(E->h_order.p);
-    size_order(rest.data(), rest.size(), ho2);
-    CU_TRY(cudaMemcpyAsync(E->d_items.p, rest.data(), rest.size() * sizeof(rest[0]), cudaMemcpyHostToDevice, st), "H2D descriptors");
-    CU_TRY(cudaMemcpyAsync(E->d_order.p, ho2, rest.size() * sizeof(*ho2), cudaMemcpyHostToDevice, st), "H2D order");
-    if (launch_batch_any(E->sms, static_cast<infl_batch_item_t*>(E->d_items.p), static_cast<uint32_t*>(E->d_order.p),
-                         rest.size(), flags, static_cast<infl_batch_result_t*>(E->d_results.p), E->d_ws.p, st) != UNZ_OK)
-      return UNZ_ERR;
-    CU_TRY(cudaMemcpyAsync(rr.data(), E->d_results.p, rr.size() * sizeof(rr[0]), cudaMemcpyDeviceToHost, st), "D2H results");
-    const auto t0 = std::chrono::steady_clock::now();
-    CU_TRY(cudaStreamSynchronize(st), "inflate kernel");
-    if (std::getenv("DEFL_SPLIT_TRACE"))
-      std::fprintf(stderr, "[split] warp-per-stream kernel, %zu streams (%zu sent back by the split path) %8.3f ms\n", rest.size(),
-                   rest.size() - (n - sin.size()), std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count());
-    for (size_t k = 0; k < rr.size(); k++) results[rest_idx[k]] = rr[k];
+    if (!back.empty()) {
+      std::vector<infl_batch_result_t> rr(back.size());
+      auto* ho2 = static_cast<uint32_t*>(E->h_order.p);
+      size_order(back.data(), back.size(), ho2);
+      CU_TRY(cudaMemcpyAsync(E->d_items.p, back.data(), back.size() * sizeof(back[0]), cudaMemcpyHostToDevice, st), "H2D descriptors");
+      CU_TRY(cudaMemcpyAsync(E->d_order.p, ho2, back.size() * sizeof(*ho2), cudaMemcpyHostToDevice, st), "H2D order");
+      if (launch_batch_any(E->sms, static_cast<infl_batch_item_t*>(E->d_items.p), static_cast<uint32_t*>(E->d_order.p),
+                           back.size(), flags, static_cast<infl_batch_result_t*>(E->d_results.p), E->d_ws.p, st) != UNZ_OK)
+        return UNZ_ERR;
+      CU_TRY(cudaMemcpyAsync(rr.data(), E->d_results.p, rr.size() * sizeof(rr[0]), cudaMemcpyDeviceToHost, st), "D2H results");
+      CU_TRY(cudaStreamSynchronize(st), "inflate kernel");
+      for (size_t k = 0; k < rr.size(); k++) results[back_idx[k]] = rr[k];
+    }
+    if (trace) {
+      auto ms = [](std::chrono::steady_clock::time_point a, std::chrono::steady_clock::time_point b) {
+        return std::chrono::duration<double, std::milli>(b - a).count();
+      };
+      std::fprintf(stderr, "[split] batch: %zu members on one warp each beside %zu split-decoded: split path done at %.3f ms, "
+                           "one-warp kernel at %.3f ms, %zu given back done at %.3f ms\n", rest.size(), sin.size() - back.size(),
+                   ms(t_begin, t_split), ms(t_begin, t_rest), back.size(), ms(t_begin, std::chrono::steady_clock::now()));
+    }
     return UNZ_OK;
   }
   auto* ho = static_cast<uint32_t*>(E->h_order.p);

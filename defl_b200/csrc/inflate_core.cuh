@@ -154,6 +154,7 @@ DEFL_DEV void adler_range(const Lane<G>& L, const uint8_t* dst, uint32_t from, u
       for (uint32_t j = tail0; j < n; j++) { uint32_t b = p[j]; ta += b; tw += j * b; }
     }
     const uint32_t* pw = reinterpret_cast<const uint32_t*>(p + head);
+#pragma unroll 8
     for (uint32_t k = L.lane; k < nwords; k += G) {
       const uint32_t v = pw[k];
       const uint32_t s = simt::dp4a(v, 0x01010101u, 0u);
@@ -186,11 +187,30 @@ DEFL_DEV void copy_from_input(const Lane<G>& L, uint8_t* d, const uint8_t* s, ui
   const uint32_t  sh = (uint32_t)((uintptr_t)s & 3u) * 8u;
   const uint32_t* sw = reinterpret_cast<const uint32_t*>((uintptr_t)s & ~(uintptr_t)3);
   uint32_t*       dw = reinterpret_cast<uint32_t*>(d);
+  // eight independent loads per lane before the first store: one warp alone on a multi-megabyte stored
+  // stream is bound by load latency, not by issue
+  constexpr uint32_t U = 8;
+  uint32_t k = L.lane;
   if (sh == 0) {
-    for (uint32_t k = L.lane; k < nw; k += G) dw[k] = simt::ld_in32(sw + k);
+#pragma unroll 1
+    for (; k + (U - 1u) * G < nw; k += U * G) {
+      uint32_t v[U];
+#pragma unroll
+      for (uint32_t u = 0; u < U; u++) v[u] = simt::ld_in32(sw + k + u * G);
+#pragma unroll
+      for (uint32_t u = 0; u < U; u++) dw[k + u * G] = v[u];
+    }
+    for (; k < nw; k += G) dw[k] = simt::ld_in32(sw + k);
   } else {
-    for (uint32_t k = L.lane; k < nw; k += G)
-      dw[k] = simt::funnel_r(simt::ld_in32(sw + k), simt::ld_in32(sw + k + 1), sh);
+#pragma unroll 1
+    for (; k + (U - 1u) * G < nw; k += U * G) {
+      uint32_t a[U], b[U];
+#pragma unroll
+      for (uint32_t u = 0; u < U; u++) { a[u] = simt::ld_in32(sw + k + u * G); b[u] = simt::ld_in32(sw + k + u * G + 1); }
+#pragma unroll
+      for (uint32_t u = 0; u < U; u++) dw[k + u * G] = simt::funnel_r(a[u], b[u], sh);
+    }
+    for (; k < nw; k += G) dw[k] = simt::funnel_r(simt::ld_in32(sw + k), simt::ld_in32(sw + k + 1), sh);
   }
   for (uint32_t j = (nw << 2) + L.lane; j < n; j += G) d[j] = simt::ld_in8(s + j);
 }

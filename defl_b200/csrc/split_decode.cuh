@@ -229,10 +229,14 @@ DEFL_DEV uint64_t fixed_probe_lane(const uint16_t* lit, const uint16_t* dist, co
     const uint64_t left = end_bit - r;
     const uint32_t s = decode_token(lit, dist, br, left > 0x7FFFFFFFull ? 0x7FFFFFFFu : (uint32_t)left, false, tok, used);
     if (s == LS_OK) { r += used; br.consume(used); continue; }
-    if (s != LS_EOB) return kNoCandidate;
+    // Not yet on the true trajectory, the bits may spell a code that does not exist or an end-of-block that is
+    // none: step one bit and go on, the trajectory is still to be met.  (A true end of block that is followed by
+    // the final block or by one that is not fixed also lands here; what the probe reports after that is a wrong
+    // guess, which costs one chunk nobody links to.)
+    if (s != LS_EOB) { r += 1u; br.consume(1u); continue; }
     r += used; br.consume(used);
     const uint32_t hdr = simt::funnel_r(br.w0, br.w1, br.bo) & 7u;       // BFINAL, BTYPE of the next block
-    if ((hdr & 1u) || ((hdr >> 1) & 3u) != 1u) return kNoCandidate;
+    if ((hdr & 1u) || ((hdr >> 1) & 3u) != 1u) continue;
     r += 3u; br.consume(3u);
   }
 }
