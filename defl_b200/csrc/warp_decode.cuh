@@ -357,13 +357,18 @@ template <> struct SymWord<uint16_t> { static constexpr uint32_t kPer = 2, kShif
 #ifndef DEFL_LANE_WORDS
 #define DEFL_LANE_WORDS 4
 #endif
-constexpr uint32_t kLaneWords = DEFL_LANE_WORDS;      // a lane copies matches of up to this many words' worth of symbols itself
+#ifndef DEFL_LANE_WORDS16
+#define DEFL_LANE_WORDS16 4
+#endif
+// a lane copies matches of up to this many words' worth of symbols itself (bytes / 16-bit symbols)
+template <typename SYM> struct LaneWords { static constexpr uint32_t k = sizeof(SYM) == 2 ? DEFL_LANE_WORDS16 : DEFL_LANE_WORDS; };
 
 template <typename SYM>
 DEFL_DEV uint32_t resolve_tokens(uint16_t* stage_mem, int lane, const uint32_t* toks, uint32_t count, SYM* dst0,
                                  uint32_t cap, uint32_t& P, uint32_t hist) {
   using SW = SymWord<SYM>;
   constexpr uint32_t kPer = SW::kPer;
+  constexpr uint32_t kLaneWords = LaneWords<SYM>::k;
   constexpr uint32_t kRoom = (uint32_t)(kStageV3 * sizeof(uint16_t) / sizeof(SYM)) - kPer;   // symbols per batch
   SYM* const      st  = reinterpret_cast<SYM*>(stage_mem);
   uint32_t* const stw = reinterpret_cast<uint32_t*>(stage_mem);
