@@ -321,8 +321,8 @@ int split_decode_many(Engine* E, const SplitInput* in, size_t nin, int flags, vo
     std::fprintf(stderr, "[split] %-28s %8.3f ms\n", what, std::chrono::duration<double, std::milli>(t - tprev).count());
     tprev = t;
   };
-  static const uint32_t granule = env_u32("DEFL_SPLIT_GRANULE", 32768u, 4096u, 1u << 24);
-  static const uint64_t min_gap = (uint64_t)env_u32("DEFL_SPLIT_GAP", 40960u, 0u, 1u << 28) * 8u;   // bits
+  static const uint32_t granule = env_u32("DEFL_SPLIT_GRANULE", 65536u, 4096u, 1u << 24);
+  static const uint64_t min_gap = (uint64_t)env_u32("DEFL_SPLIT_GAP", 0u, 0u, 1u << 28) * 8u;   // bits
   static const uint32_t tok_per_byte = env_u32("DEFL_SPLIT_TOKENS_PER_BYTE", 3u, 0u, 32u);
   static const bool     fixed_mid = env_u32("DEFL_SPLIT_FIXED", 1u, 0u, 1u) != 0u;
   static const uint32_t probe_bits = env_u32("DEFL_SPLIT_PROBE_BITS", 16384u, 256u, 1u << 20);
