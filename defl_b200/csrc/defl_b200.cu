@@ -262,11 +262,12 @@ int launch_batch_any(int sms, const infl_batch_item_t* d_items, const uint32_t* 
   }
 }
 
-// largest compressed stream first: the longest serial decode starts earliest
+// longest serial decode first.  The work of a stream is its tokens (about its compressed size) plus its
+// output words: a few KiB that expand to megabytes of one repeated byte are not a short job.
 void size_order(const infl_batch_item_t* items, size_t n, uint32_t* order) {
   std::iota(order, order + n, 0u);
-  std::stable_sort(order, order + n,
-                   [&](uint32_t a, uint32_t b) { return items[a].srclen > items[b].srclen; });
+  auto work = [&](uint32_t i) { return items[i].srclen + (items[i].dstlen >> 4); };
+  std::stable_sort(order, order + n, [&](uint32_t a, uint32_t b) { return work(a) > work(b); });
 }
 
 constexpr size_t kAlign = 16;
