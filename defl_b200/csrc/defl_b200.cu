@@ -326,7 +326,7 @@ int split_decode_many(Engine* E, const SplitInput* in, size_t nin, int flags, vo
   static const uint64_t min_gap = (uint64_t)env_u32("DEFL_SPLIT_GAP", 0u, 0u, 1u << 28) * 8u;   // bits
   static const uint32_t tok_per_byte = env_u32("DEFL_SPLIT_TOKENS_PER_BYTE", 3u, 0u, 32u);
   static const bool     fixed_mid = env_u32("DEFL_SPLIT_FIXED", 1u, 0u, 1u) != 0u;
-  static const uint32_t probe_bits = env_u32("DEFL_SPLIT_PROBE_BITS", 16384u, 256u, 1u << 20);
+  static const uint32_t probe_bits = env_u32("DEFL_SPLIT_PROBE_BITS", 32768u, 256u, 1u << 20);
 
   int grid_warps = 0;
   if (warp_kernel_grid(E->sms, &grid_warps) != UNZ_OK) return UNZ_ERR;      // CTAs of kWarpsPerCta warps
