@@ -207,10 +207,46 @@ int warp_kernel_grid(int sms, int* grid_out) {
   return UNZ_OK;
 }
 
+// ---- v4 (default engine): warp per stream, 64-bit tokens, shared-memory rings and stage ----------------------
+int warp4_kernel_grid(int sms, int* grid_out) {
+  auto         kern = defl::inflate_warp4_kernel<kWarpsPerCta>;
+  const size_t smem = sizeof(defl::v4::WarpSmem4) * kWarpsPerCta;
+  static int   ctas_per_sm[kMaxDevices] = {0};
+  int          dev = 0;
+  cudaGetDevice(&dev);
+  if (!ctas_per_sm[dev]) {
+    CU_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem),
+           "cudaFuncSetAttribute(smem)");
+    int occ = 0;
+    CU_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, kWarpsPerCta * 32, smem), "occupancy query");
+    if (occ < 1) return fail("inflate warp4 kernel does not fit on an SM");
+    ctas_per_sm[dev] = occ;
+  }
+  *grid_out = sms * ctas_per_sm[dev];
+  return UNZ_OK;
+}
+
+// one workspace serves whichever engine runs: the larger of the two
 size_t warp_kernel_workspace(int sms) {
+  int grid = 0, grid4 = 0;
+  if (warp_kernel_grid(sms, &grid) != UNZ_OK || warp4_kernel_grid(sms, &grid4) != UNZ_OK) return 0;
+  return kWsHeader + std::max((size_t)grid * kWarpsPerCta * defl::kWarpScratchBytes,
+                              (size_t)grid4 * kWarpsPerCta * defl::v4::kWarpScratchBytes);
+}
+
+int launch_warp4(int sms, const infl_batch_item_t* d_items, const uint32_t* d_order, uint32_t n, int flags,
+                 infl_batch_result_t* d_results, void* d_ws, cudaStream_t st) {
   int grid = 0;
-  if (warp_kernel_grid(sms, &grid) != UNZ_OK) return 0;
-  return kWsHeader + (size_t)grid * kWarpsPerCta * defl::kWarpScratchBytes;
+  if (warp4_kernel_grid(sms, &grid) != UNZ_OK) return UNZ_ERR;
+  grid = (int)std::max<uint64_t>(1, std::min<uint64_t>((uint64_t)grid, (n + kWarpsPerCta - 1) / kWarpsPerCta));
+  auto* ticket  = static_cast<unsigned int*>(d_ws);
+  auto* scratch = static_cast<unsigned char*>(d_ws) + kWsHeader;
+  CU_TRY(cudaMemsetAsync(ticket, 0, sizeof(unsigned int), st), "cudaMemsetAsync(ticket)");
+  defl::inflate_warp4_kernel<kWarpsPerCta><<<(unsigned)grid, kWarpsPerCta * 32, sizeof(defl::v4::WarpSmem4) * kWarpsPerCta, st>>>(
+      d_items, d_order, n, flags, d_results, ticket, scratch);
+  CU_TRY(cudaGetLastError(), "inflate_warp4_kernel launch");
+  g_launches.fetch_add(1, std::memory_order_relaxed);
+  return UNZ_OK;
 }
 
 int launch_warp(int sms, const infl_batch_item_t* d_items, const uint32_t* d_order, uint32_t n, int flags,
@@ -228,7 +264,7 @@ int launch_warp(int sms, const infl_batch_item_t* d_items, const uint32_t* d_ord
   return UNZ_OK;
 }
 
-std::atomic<int> g_engine{3};   // 3 = warp per stream (default), 2 = lane-decoder pipeline, 1 = group per stream
+std::atomic<int> g_engine{4};   // 4 = warp per stream v4 (default), 3 = v3, 2 = lane-decoder pipeline, 1 = group per stream
 
 int launch_batch_any(int sms, const infl_batch_item_t* d_items, const uint32_t* d_order, size_t n, int flags,
                      infl_batch_result_t* d_results, void* d_ws, cudaStream_t st) {
@@ -236,6 +272,8 @@ int launch_batch_any(int sms, const infl_batch_item_t* d_items, const uint32_t* 
   if (n > 0xFFFFFFFFull) return fail("batch too large (n must fit 32 bits)");
   int  lanes = g_lanes_per_stream.load();
   auto t = static_cast<unsigned int*>(d_ws);
+  if (!lanes && g_engine.load() == 4)
+    return launch_warp4(sms, d_items, d_order, (uint32_t)n, flags, d_results, d_ws, st);
   if (!lanes && g_engine.load() == 3)
     return launch_warp(sms, d_items, d_order, (uint32_t)n, flags, d_results, d_ws, st);
   if (!lanes) {   // the lane-decoder pipeline (v2)
@@ -1071,9 +1109,10 @@ UNZ_EXPORT const char* infl_engine_info(void) {
                 "defl_b200 %d.%d sm_100a; engine=%d (%s); lanes/stream=%d; smem/warp=%zu B; window<=32x%u bits; "
                 "lit root %d bits, dist root %d bits",
                 DEFL_B200_VERSION_MAJOR, DEFL_B200_VERSION_MINOR, engine,
-                engine == 3 ? "warp per stream, speculative sub-sequences" : engine == 2 ? "lane-decoder pipeline"
-                                                                                          : "group per stream",
-                lanes, sizeof(defl::WarpSmem), defl::kSubMax, defl::kLitRootBits, defl::kDistRootBits);
+                engine == 4 ? "warp per stream v4: literals+match tokens, smem rings and stage"
+                : engine == 3 ? "warp per stream, speculative sub-sequences" : engine == 2 ? "lane-decoder pipeline"
+                                                                                            : "group per stream",
+                lanes, engine == 4 ? sizeof(defl::v4::WarpSmem4) : sizeof(defl::WarpSmem), defl::kSubMax, defl::kLitRootBits, defl::kDistRootBits);
   return buf;
 }
 
@@ -1100,7 +1139,7 @@ UNZ_EXPORT size_t infl_batch_workspace_size(size_t n) {
 }
 
 UNZ_EXPORT int infl_set_engine(int engine) {
-  if (engine < 1 || engine > 3) return fail("engine must be 1 (group per stream), 2 (lane-decoder pipeline) or 3 (warp per stream)");
+  if (engine < 1 || engine > 4) return fail("engine must be 1 (group per stream), 2 (lane-decoder pipeline), 3 (warp per stream, v3) or 4 (v4)");
   g_engine.store(engine);
   return UNZ_OK;
 }

@@ -265,7 +265,9 @@ DEFL_DEV uint32_t dist_entry(uint32_t sym, uint32_t len) {
 
 // Build one decode table from code lengths.  Accept/reject exactly as infl_ft_build
 // (infl.c:478-490): over-subscribed => false; incomplete or empty => true.
-template <int G, int ROOT_BITS, int TAB, bool IS_DIST>
+// EMPTY: what a slot no code maps to holds (0; the v4 decoder asks for kLitEob with 0 code bits in the
+// literal/length table, so that "not a plain literal" is one test)
+template <int G, int ROOT_BITS, int TAB, bool IS_DIST, uint32_t EMPTY = 0u>
 DEFL_DEV bool build_table(const Lane<G>& L, BuildScratch& sm, uint16_t* tab, const uint8_t* lens,
                           uint32_t n) {
   constexpr uint32_t ROOT = 1u << ROOT_BITS;
@@ -310,7 +312,7 @@ DEFL_DEV bool build_table(const Lane<G>& L, BuildScratch& sm, uint16_t* tab, con
 
   {
     uint32_t* t32 = reinterpret_cast<uint32_t*>(tab);
-    for (uint32_t i = L.lane; i < (total + 1u) / 2u; i += G) t32[i] = 0u;
+    for (uint32_t i = L.lane; i < (total + 1u) / 2u; i += G) t32[i] = EMPTY | (EMPTY << 16);
   }
   simt::syncwarp(L.gmask);
 
@@ -331,7 +333,8 @@ DEFL_DEV bool build_table(const Lane<G>& L, BuildScratch& sm, uint16_t* tab, con
     if (!l) continue;
 
     const uint32_t cd    = c0 + rank;
-    const uint32_t entry = IS_DIST ? dist_entry(s, l) : lit_entry(s, l);
+    uint32_t entry = IS_DIST ? dist_entry(s, l) : lit_entry(s, l);
+    if (EMPTY != 0u && entry == 0u) entry = EMPTY;
     if (l <= (uint32_t)ROOT_BITS) {
       const uint32_t r = simt::brev(cd) >> (32u - l);
       for (uint32_t i = r; i < ROOT; i += 1u << l) tab[i] = (uint16_t)entry;
@@ -416,7 +419,7 @@ DEFL_DEV uint32_t stored_block(const Lane<G>& L, BitReader& br, const uint8_t* s
 
 // Fixed (btype 1) or dynamic (btype 2) block: leave decode tables for it in lit/dist.
 // `br` stands right after the 3 header bits.  Returns a Reason.
-template <int G>
+template <int G, uint32_t EMPTY = 0u>
 DEFL_DEV uint32_t huffman_block_setup(const Lane<G>& L, uint16_t* lit, uint16_t* dist, BuildScratch& s,
                                       BitReader& br, uint64_t end_bit, uint32_t btype, bool& fixed_ready) {
   if (btype == 1) {
@@ -426,7 +429,7 @@ DEFL_DEV uint32_t huffman_block_setup(const Lane<G>& L, uint16_t* lit, uint16_t*
       for (uint32_t i = L.lane; i < 320u; i += G)
         s.lens[i] = i < 144u ? 8 : i < 256u ? 9 : i < 280u ? 7 : i < 288u ? 8 : 5;
       simt::syncwarp(L.gmask);
-      build_table<G, kLitRootBits, kLitTab, false>(L, s, lit, s.lens, 288u);
+      build_table<G, kLitRootBits, kLitTab, false, EMPTY>(L, s, lit, s.lens, 288u);
       build_table<G, kDistRootBits, kDistTab, true>(L, s, dist, s.lens + 288, 32u);
       fixed_ready = true;
     }
@@ -493,7 +496,7 @@ DEFL_DEV uint32_t huffman_block_setup(const Lane<G>& L, uint16_t* lit, uint16_t*
   }
   if (reason) return reason;
   simt::syncwarp(L.gmask);
-  if (!build_table<G, kLitRootBits, kLitTab, false>(L, s, lit, s.lens, hlit) ||
+  if (!build_table<G, kLitRootBits, kLitTab, false, EMPTY>(L, s, lit, s.lens, hlit) ||
       !build_table<G, kDistRootBits, kDistTab, true>(L, s, dist, s.lens + hlit, hdist))
     return R_TABLE;
   return R_NONE;

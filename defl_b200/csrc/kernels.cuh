@@ -4,6 +4,7 @@
 #include "inflate_core.cuh"
 #include "pipeline.cuh"
 #include "warp_decode.cuh"
+#include "warp_decode4.cuh"
 #include "split_decode.cuh"
 #include "../../include/defl/infl_batch.h"
 
@@ -117,6 +118,46 @@ inflate_warp_kernel(const infl_batch_item_t* __restrict__ items, const uint32_t*
     } else {
       inflate_stream_warp(sm, sc, lane, static_cast<const uint8_t*>(it.src), (uint32_t)it.srclen,
                           static_cast<uint8_t*>(it.dst), (uint32_t)it.dstlen, flags, o);
+    }
+    if (lane == 0) {
+      infl_batch_result_t r;
+      r.code = o.code; r.adler = o.adler; r.outlen = o.outlen; r.inpos = o.inpos;
+      r.adler_stored = o.adler_stored; r.info = o.info;
+      results[idx] = r;
+    }
+    simt::syncwarp(kFull);
+  }
+}
+
+// K3 (v4, default): one warp per stream, 64-bit "literals + match" tokens, shared-memory input rings and
+// output stage (warp_decode4.cuh).  Persistent CTAs of WARPS warps; each warp owns a slice of the global
+// token scratch and pulls streams from the ticket counter.
+#ifndef DEFL_WARP4_CTAS_PER_SM
+#define DEFL_WARP4_CTAS_PER_SM 6
+#endif
+template <int WARPS>
+__global__ void __launch_bounds__(WARPS * 32, DEFL_WARP4_CTAS_PER_SM)
+inflate_warp4_kernel(const infl_batch_item_t* __restrict__ items, const uint32_t* __restrict__ order,
+                     uint32_t n, int flags, infl_batch_result_t* __restrict__ results,
+                     unsigned int* __restrict__ ticket, unsigned char* __restrict__ scratch) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  v4::WarpSmem4&         sm = reinterpret_cast<v4::WarpSmem4*>(smem_raw)[warp];
+  const v4::WarpScratch4 sc = v4::scratch4_of(scratch + ((size_t)blockIdx.x * WARPS + warp) * v4::kWarpScratchBytes);
+
+  for (;;) {
+    uint32_t k = 0;
+    if (lane == 0) k = atomicAdd(ticket, 1u);
+    k = simt::shfl(kFull, k, 0);
+    if (k >= n) break;
+    const uint32_t idx = order ? order[k] : k;
+    const infl_batch_item_t it = items[idx];
+    StreamOut o;
+    if (it.srclen > 0xFFFFFFFFull || it.dstlen > 0xFFFFFFFFull) {
+      o.code = -1; o.adler = 1; o.outlen = 0; o.inpos = 0; o.adler_stored = 0; o.info = R_TRUNCATED << 8;
+    } else {
+      v4::inflate_stream_warp4(sm, sc, lane, static_cast<const uint8_t*>(it.src), (uint32_t)it.srclen,
+                               static_cast<uint8_t*>(it.dst), (uint32_t)it.dstlen, flags, o);
     }
     if (lane == 0) {
       infl_batch_result_t r;

@@ -89,4 +89,15 @@ DEFL_DEV void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "mem
 template <int N>
 DEFL_DEV void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 
+// ---- used by the v4 warp decoder (warp_decode4.cuh) ---------------------------------------------------
+// 64-bit tokens written by one lane, read back by the whole warp: L2 only
+DEFL_DEV uint2 ld_tok2(const uint2* p) { return __ldcg(p); }
+// global -> shared, 16 bytes, of which only the first `nbytes` (0..16) are read; the rest is zero-filled
+DEFL_DEV void cp_async16_n(void* smem_dst, const void* gsrc, uint32_t nbytes) {
+  const unsigned s = (unsigned)__cvta_generic_to_shared(smem_dst);
+  const size_t   g = __cvta_generic_to_global(gsrc);
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(s), "l"(g), "r"(nbytes) : "memory");
+}
+DEFL_DEV uint4 ld_out128(const uint4* p) { return __ldcg(p); }
+
 }  // namespace simt

@@ -4,6 +4,7 @@
 #include "../../defl_b200/csrc/inflate_core.cuh"
 #include "../../defl_b200/csrc/pipeline.cuh"
 #include "../../defl_b200/csrc/warp_decode.cuh"
+#include "../../defl_b200/csrc/warp_decode4.cuh"
 
 #include <stdlib.h>
 #include <vector>
@@ -180,6 +181,53 @@ extern "C" int emu_warp_inflate(const uint8_t* src, uint32_t srclen, uint8_t* ds
   for (int i = 0; i < 32; i++) jobs[i] = WarpJob{&grp, i, sm, scratch, src, srclen, dst, cap, flags, out};
   for (int i = 1; i < 32; i++) pthread_create(&th[i], nullptr, warp_main, &jobs[i]);
   warp_main(&jobs[0]);
+  for (int i = 1; i < 32; i++) pthread_join(th[i], nullptr);
+  pthread_barrier_destroy(&grp.bar);
+  free(sm); free(scratch);
+  return out->code;
+}
+
+// ---- one emulated warp of the v4 warp-per-stream decoder (warp_decode4.cuh) ------------------------------
+namespace {
+struct Warp4Job {
+  simt::Group*           grp;
+  int                    lane;
+  defl::v4::WarpSmem4*   sm;
+  void*                  scratch;
+  const uint8_t*         src;
+  uint32_t               srclen;
+  uint8_t*               dst;
+  uint32_t               cap;
+  int                    flags;
+  defl::StreamOut*       out;
+};
+void* warp4_main(void* arg) {
+  Warp4Job* j = static_cast<Warp4Job*>(arg);
+  simt::t_group = j->grp;
+  simt::t_lane  = j->lane;
+  defl::StreamOut o;
+  defl::v4::inflate_stream_warp4(*j->sm, defl::v4::scratch4_of(j->scratch), j->lane, j->src, j->srclen, j->dst,
+                                 j->cap, j->flags, o);
+  if (j->lane == 0) *j->out = o;
+  return nullptr;
+}
+}  // namespace
+
+extern "C" int emu_warp4_inflate(const uint8_t* src, uint32_t srclen, uint8_t* dst, uint32_t cap, int flags,
+                                 defl::StreamOut* out) {
+  simt::Group grp;
+  grp.G = 32;
+  pthread_barrier_init(&grp.bar, nullptr, 32);
+  using defl::v4::WarpSmem4;
+  WarpSmem4* sm = static_cast<WarpSmem4*>(aligned_alloc(64, (sizeof(WarpSmem4) + 63) & ~63ul));
+  memset(sm, 0xA5, sizeof(*sm));
+  void* scratch = aligned_alloc(64, defl::v4::kWarpScratchBytes);
+  memset(scratch, 0x5A, defl::v4::kWarpScratchBytes);
+  std::vector<Warp4Job>  jobs(32);
+  std::vector<pthread_t> th(32);
+  for (int i = 0; i < 32; i++) jobs[i] = Warp4Job{&grp, i, sm, scratch, src, srclen, dst, cap, flags, out};
+  for (int i = 1; i < 32; i++) pthread_create(&th[i], nullptr, warp4_main, &jobs[i]);
+  warp4_main(&jobs[0]);
   for (int i = 1; i < 32; i++) pthread_join(th[i], nullptr);
   pthread_barrier_destroy(&grp.bar);
   free(sm); free(scratch);

@@ -148,4 +148,23 @@ inline void cp_async16(void* smem_dst, const void* gsrc, bool valid) {
 inline void cp_async_commit() {}
 template <int N> inline void cp_async_wait() {}
 
+inline uint32_t byte_perm(uint32_t a, uint32_t b, uint32_t s) {
+  const uint64_t v = ((uint64_t)b << 32) | a;
+  uint32_t r = 0;
+  for (int i = 0; i < 4; i++) r |= (uint32_t)((v >> (8 * ((s >> (4 * i)) & 7u))) & 0xFFu) << (8 * i);
+  return r;
+}
+}  // namespace simt
+struct uint2 { uint32_t x, y; };
+struct uint4 { uint32_t x, y, z, w; };
+inline uint2 make_uint2(uint32_t x, uint32_t y) { uint2 r; r.x = x; r.y = y; return r; }
+inline uint4 make_uint4(uint32_t x, uint32_t y, uint32_t z, uint32_t w) { uint4 r; r.x = x; r.y = y; r.z = z; r.w = w; return r; }
+namespace simt {
+inline uint2 ld_tok2(const uint2* p) { uint2 r; r.x = *(const volatile uint32_t*)&p->x; r.y = *(const volatile uint32_t*)&p->y; return r; }
+inline void cp_async16_n(void* smem_dst, const void* gsrc, uint32_t nbytes) {
+  memset(smem_dst, 0, 16);
+  if (nbytes) memcpy(smem_dst, gsrc, nbytes > 16 ? 16 : nbytes);
+}
+inline uint4 ld_out128(const uint4* p) { uint4 r; memcpy(&r, p, 16); return r; }
+
 }  // namespace simt

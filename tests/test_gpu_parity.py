@@ -311,7 +311,7 @@ def test_pipeline_shapes(gpu_lib):
                 assert int(res[i]["adler"]) == (zlib.adler32(raw) & 0xFFFFFFFF)
     finally:
         d.set_pipeline_shape(0)
-        d.set_engine(3)
+        d.set_engine(4)
 
 
 def test_split_single_large_stream(gpu_lib):
