@@ -208,17 +208,14 @@ int warp_kernel_grid(int sms, int* grid_out) {
 }
 
 // ---- v4 (default engine): warp per stream, 64-bit tokens, shared-memory rings and stage ----------------------
-int warp4_kernel_grid(int sms, int* grid_out) {
-  auto         kern = defl::inflate_warp4_kernel<kWarpsPerCta>;
-  const size_t smem = sizeof(defl::v4::WarpSmem4) * kWarpsPerCta;
-  static int   ctas_per_sm[kMaxDevices] = {0};
-  int          dev = 0;
+int warp4_kernel_grid(int sms, int* grid_out) {        // in warps = CTAs
+  auto       kern = defl::inflate_warp4_kernel;
+  static int ctas_per_sm[kMaxDevices] = {0};
+  int        dev = 0;
   cudaGetDevice(&dev);
   if (!ctas_per_sm[dev]) {
-    CU_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem),
-           "cudaFuncSetAttribute(smem)");
     int occ = 0;
-    CU_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, kWarpsPerCta * 32, smem), "occupancy query");
+    CU_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, 32, 0), "occupancy query");
     if (occ < 1) return fail("inflate warp4 kernel does not fit on an SM");
     ctas_per_sm[dev] = occ;
   }
@@ -231,19 +228,18 @@ size_t warp_kernel_workspace(int sms) {
   int grid = 0, grid4 = 0;
   if (warp_kernel_grid(sms, &grid) != UNZ_OK || warp4_kernel_grid(sms, &grid4) != UNZ_OK) return 0;
   return kWsHeader + std::max((size_t)grid * kWarpsPerCta * defl::kWarpScratchBytes,
-                              (size_t)grid4 * kWarpsPerCta * defl::v4::kWarpScratchBytes);
+                              (size_t)grid4 * defl::v4::kWarpScratchBytes);
 }
 
 int launch_warp4(int sms, const infl_batch_item_t* d_items, const uint32_t* d_order, uint32_t n, int flags,
                  infl_batch_result_t* d_results, void* d_ws, cudaStream_t st) {
   int grid = 0;
   if (warp4_kernel_grid(sms, &grid) != UNZ_OK) return UNZ_ERR;
-  grid = (int)std::max<uint64_t>(1, std::min<uint64_t>((uint64_t)grid, (n + kWarpsPerCta - 1) / kWarpsPerCta));
+  grid = (int)std::max<uint64_t>(1, std::min<uint64_t>((uint64_t)grid, n));
   auto* ticket  = static_cast<unsigned int*>(d_ws);
   auto* scratch = static_cast<unsigned char*>(d_ws) + kWsHeader;
   CU_TRY(cudaMemsetAsync(ticket, 0, sizeof(unsigned int), st), "cudaMemsetAsync(ticket)");
-  defl::inflate_warp4_kernel<kWarpsPerCta><<<(unsigned)grid, kWarpsPerCta * 32, sizeof(defl::v4::WarpSmem4) * kWarpsPerCta, st>>>(
-      d_items, d_order, n, flags, d_results, ticket, scratch);
+  defl::inflate_warp4_kernel<<<(unsigned)grid, 32, 0, st>>>(d_items, d_order, n, flags, d_results, ticket, scratch);
   CU_TRY(cudaGetLastError(), "inflate_warp4_kernel launch");
   g_launches.fetch_add(1, std::memory_order_relaxed);
   return UNZ_OK;
@@ -264,7 +260,7 @@ int launch_warp(int sms, const infl_batch_item_t* d_items, const uint32_t* d_ord
   return UNZ_OK;
 }
 
-std::atomic<int> g_engine{4};   // 4 = warp per stream v4 (default), 3 = v3, 2 = lane-decoder pipeline, 1 = group per stream
+std::atomic<int> g_engine{3};   // 3 = warp per stream (default), 4 = v4 (selectable; not faster yet), 2 = lane-decoder pipeline, 1 = group per stream
 
 int launch_batch_any(int sms, const infl_batch_item_t* d_items, const uint32_t* d_order, size_t n, int flags,
                      infl_batch_result_t* d_results, void* d_ws, cudaStream_t st) {

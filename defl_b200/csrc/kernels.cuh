@@ -130,20 +130,20 @@ inflate_warp_kernel(const infl_batch_item_t* __restrict__ items, const uint32_t*
 }
 
 // K3 (v4, default): one warp per stream, 64-bit "literals + match" tokens, shared-memory input rings and
-// output stage (warp_decode4.cuh).  Persistent CTAs of WARPS warps; each warp owns a slice of the global
-// token scratch and pulls streams from the ticket counter.
+// output stage (warp_decode4.cuh).  Persistent CTAs of ONE warp: its shared memory is then a static object at
+// constant addresses (every table lookup is "LDS [R + imm]", nothing is rematerialised from threadIdx), and
+// up to 32 such CTAs are resident per SM.  Each warp owns a slice of the global token scratch and pulls
+// streams from the ticket counter.
 #ifndef DEFL_WARP4_CTAS_PER_SM
-#define DEFL_WARP4_CTAS_PER_SM 6
+#define DEFL_WARP4_CTAS_PER_SM 24
 #endif
-template <int WARPS>
-__global__ void __launch_bounds__(WARPS * 32, DEFL_WARP4_CTAS_PER_SM)
+__global__ void __launch_bounds__(32, DEFL_WARP4_CTAS_PER_SM)
 inflate_warp4_kernel(const infl_batch_item_t* __restrict__ items, const uint32_t* __restrict__ order,
                      uint32_t n, int flags, infl_batch_result_t* __restrict__ results,
                      unsigned int* __restrict__ ticket, unsigned char* __restrict__ scratch) {
-  extern __shared__ __align__(16) unsigned char smem_raw[];
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  v4::WarpSmem4&         sm = reinterpret_cast<v4::WarpSmem4*>(smem_raw)[warp];
-  const v4::WarpScratch4 sc = v4::scratch4_of(scratch + ((size_t)blockIdx.x * WARPS + warp) * v4::kWarpScratchBytes);
+  __shared__ __align__(16) v4::WarpSmem4 sm;
+  const int lane = threadIdx.x;
+  const v4::WarpScratch4 sc = v4::scratch4_of(scratch + (size_t)blockIdx.x * v4::kWarpScratchBytes);
 
   for (;;) {
     uint32_t k = 0;

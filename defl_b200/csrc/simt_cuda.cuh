@@ -99,5 +99,6 @@ DEFL_DEV void cp_async16_n(void* smem_dst, const void* gsrc, uint32_t nbytes) {
   asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(s), "l"(g), "r"(nbytes) : "memory");
 }
 DEFL_DEV uint4 ld_out128(const uint4* p) { return __ldcg(p); }
+DEFL_DEV void  atomic_min_shared(uint32_t* p, uint32_t v) { atomicMin(p, v); }
 
 }  // namespace simt

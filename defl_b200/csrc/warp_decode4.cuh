@@ -24,18 +24,18 @@ namespace v4 {
 
 constexpr uint32_t kSubMax    = 8192;                 // bits per lane per window, at most
 constexpr uint32_t kSubMin    = 512;
-constexpr uint32_t kCpBits    = 128;                  // checkpoint spacing (a token is at most 94 bits)
+constexpr uint32_t kCpBits    = 256;                  // checkpoint spacing (a token is at most 94 bits)
 constexpr uint32_t kCpPerLane = kSubMax / kCpBits;
 constexpr uint32_t kSpecCap   = 1024;                 // tokens per lane per window (speculative pass)
 constexpr uint32_t kFixCap    = 256;                  // tokens per lane per window (fix-up pass)
-constexpr size_t   kWarpScratchBytes = 32u * (kSpecCap + kFixCap) * 8u + 32u * kCpPerLane * 4u;
+constexpr size_t   kWarpScratchBytes = 32u * (kSpecCap + kFixCap) * 8u + 32u * 96u * 4u;
 static_assert(kWarpScratchBytes % 16 == 0, "scratch slices stay 16-byte aligned");
 
 constexpr uint32_t kEmptyLit  = kLitEob;              // literal/length slots no code maps to: "end of block, 0 bits"
 constexpr uint32_t kNotLit    = kLitIsLen | kLitKind; // any of these bits: not a plain literal
 
 // token: x = [8:0] match length (0: none)  [23:9] distance - 1  [26:24] literals in front (0..4)
-//        y = the literal bytes, the LAST one in bits 31:24 (they are shifted in from the top)
+//        y = the literal bytes, the first one in bits 7:0
 DEFL_DEV uint32_t tok_len(uint32_t x)  { return x & 511u; }
 DEFL_DEV uint32_t tok_d1(uint32_t x)   { return (x >> 9) & 0x7FFFu; }
 DEFL_DEV uint32_t tok_nlit(uint32_t x) { return (x >> 24) & 7u; }
@@ -48,10 +48,12 @@ constexpr uint32_t kKeepBytes  = 1024;                // history that survives a
 struct WarpSmem4 {
   uint16_t lit[kLitTab];
   uint16_t dist[kDistTab];
+  uint32_t stop_lane;                                 // speculative pass: the lowest lane that met the end of the block
+  uint32_t pad_[3];
   union {
     BuildScratch s;                                   // while a block header is parsed
     uint32_t     ring[32 * kRingWords];               // speculative pass: the lanes' input rings
-    uint8_t      stage[kStageBytes + 16];             // resolver: output not yet in dst + recent history
+    uint8_t      stage[kStageBytes + 64];             // resolver: output not yet in dst + recent history
   };
 };
 static_assert(sizeof(WarpSmem4) % 16 == 0, "WarpSmem4 alignment");
@@ -76,24 +78,29 @@ struct Ring4 {
   uint32_t       abytes, skew;
   uint32_t       have;       // quads [.., have) have been asked for
 
+  uint32_t       qlo, qhi;   // quads [qlo, qhi) of the window lie wholly inside the input: one plain 16-byte copy each
+
   DEFL_DEV void request(uint32_t q) {
-    const uint32_t aq   = qoff + q;                               // quad index from q0
-    const uint32_t left = abytes > aq * 16u ? abytes - aq * 16u : 0u;
     uint32_t* const slot = ring + (q & 7u) * 4u;
     const uint8_t*  g    = qbase + (size_t)q * 16u;
+    if (q >= qlo && q < qhi) {
+      simt::cp_async16(slot, g, true);
+      if ((q & 7u) == 0u) simt::cp_async16(ring + 32u, g, true);
+      return;
+    }
+    request_edge(q, slot, g);
+  }
+  // the quads at the ends of the input: nothing outside [first word, last byte] is read
+  DEFL_DEV void request_edge(uint32_t q, uint32_t* slot, const uint8_t* g) {
+    const uint32_t aq   = qoff + q;                               // quad index from q0
+    const uint32_t left = abytes > aq * 16u ? abytes - aq * 16u : 0u;
     if (aq == 0u && skew != 0u) {
       // the first quad starts before the stream's first word: word by word, and nothing below that word
-#pragma unroll
+#pragma unroll 1
       for (uint32_t i = 0; i < 4; i++) {
         const bool in = i >= skew && left > i * 4u;
         simt::cp_async4(slot + i, in ? g + i * 4u : g + skew * 4u, in);
-      }
-      if ((q & 7u) == 0u) {
-#pragma unroll
-        for (uint32_t i = 0; i < 4; i++) {
-          const bool in = i >= skew && left > i * 4u;
-          simt::cp_async4(ring + 32u + i, in ? g + i * 4u : g + skew * 4u, in);
-        }
+        if ((q & 7u) == 0u) simt::cp_async4(ring + 32u + i, in ? g + i * 4u : g + skew * 4u, in);
       }
       return;
     }
@@ -104,8 +111,12 @@ struct Ring4 {
   DEFL_DEV void init(uint32_t* ring_lane, const Input4& in, uint32_t base_quad, uint32_t r) {
     ring = ring_lane; abytes = in.abytes; skew = in.skew; qoff = base_quad;
     qbase = in.q0 + (size_t)base_quad * 16u;
+    const uint32_t full = in.abytes >> 4;                         // whole quads of input, counted from q0
+    qlo = (base_quad == 0u && in.skew != 0u) ? 1u : 0u;
+    qhi = full > base_quad ? full - base_quad : 0u;
     have = r >> 7;
     const uint32_t lim = have + 8u;
+#pragma unroll 1
     for (; have < lim; have++) request(have);
     simt::cp_async_commit();
   }
@@ -148,7 +159,7 @@ DEFL_DEV uint32_t careful_token(const uint16_t* lit, const uint16_t* dist, SubRe
     }
     if (!(e & kLitIsLen)) {
       if (cl > avail) return fail_stat(R_TRUNCATED);
-      lits = simt::byte_perm(lits, e, 0x4321);
+      lits |= (e & 255u) << (8u * nlit);
       nlit++;
       used += cl; avail -= cl;
       br.consume(cl);
@@ -179,103 +190,127 @@ DEFL_DEV uint32_t careful_token(const uint16_t* lit, const uint16_t* dist, SubRe
 // ---- speculative pass: one lane, one sub-sequence -------------------------------------------------------------
 // Decodes from `start` (after a warm-up of `warm` bits in front of it whose tokens are thrown away) to the first
 // token boundary >= limit.  Positions are window-relative bits; `bw` = index in in.words of the window's word 0.
-// Every 128 bits the lane notes where a token started and how many tokens it had written (checkpoints).
+// Every lane of the warp yields one token per trip, so the trips are counted once for all: every fourth trip the
+// rings are topped up and the lane looks whether it still has to go on, every sixteenth it notes where it stands
+// (a checkpoint: position | tokens written << 20) for the fix-up pass.  Nothing of this is done per token.
+constexpr uint32_t kCpTokens = 16;
+constexpr uint32_t kCpMax    = 96;        // checkpoints per lane: (warm-up tokens + kSpecCap) / 16, rounded up
+
+// literal k of a token goes to byte k of the token's second word
+#define DEFL_LIT_SEL(k) ((k) == 0 ? 0x3214u : (k) == 1 ? 0x3240u : (k) == 2 ? 0x3410u : 0x4210u)
+
 DEFL_DEV void lane_spec4(const uint16_t* lit, const uint16_t* dist, const Input4& in, uint32_t base_quad,
                          uint32_t bw, uint32_t start, uint32_t limit, uint32_t endr, uint2* seg, uint32_t* cps,
-                         LaneTraj& tj, uint32_t warm, uint32_t* ring_lane) {
+                         LaneTraj& tj, uint32_t warm, uint32_t* ring_lane, uint32_t* stop_lane, uint32_t lane) {
   uint32_t r = start - warm, r0 = start;
   Ring4 rg;
   rg.init(ring_lane, in, base_quad, r);
-  uint32_t        next_cp = start, stat = LS_OK, it = 0;
-  uint2*          tp = seg;
-  uint2* const    tend = seg + kSpecCap;
-  uint32_t*       cpp = cps;
-  const uint32_t  fast_limit = endr >= 128u ? (limit < endr - 128u ? limit : endr - 128u) : 0u;
+  uint32_t       stat = LS_OK, trips4 = 0, ncp = 0;
+  uint32_t       ti = 0;                       // tokens kept
+  uint32_t       keep = warm == 0u ? 1u : 0u;  // 0 while warming up
+  const uint32_t fast_limit = endr >= 128u ? (limit < endr - 128u ? limit : endr - 128u) : 0u;
   for (;;) {
     // ---- fast loop: no end-of-input arithmetic (it stops 128 bits short of the end), one token per trip
     while (r < fast_limit) {
-      if ((it++ & 3u) == 0u) rg.topup(r);
-      if (r >= next_cp) {                                  // a token boundary in a new 128-bit stretch
-        if (next_cp == start) { tp = seg; r0 = r; }        // ... the first one of the sub-sequence: the warm-up ends
-        *cpp++ = (r - next_cp) | ((uint32_t)(tp - seg) << 8);
-        next_cp += kCpBits;
-      }
-      if (tp == tend) {
-        if (next_cp != start) break;
-        tp = seg;                                          // still warming up: these tokens are thrown away anyway
-      }
-      const uint32_t* p = rg.ring + ((r >> 5) & 31u);
-      const uint32_t a0 = p[0], a1 = p[1], a2 = p[2], a3 = p[3];
-      uint32_t V0 = simt::funnel_r(a0, a1, r), V1 = simt::funnel_r(a1, a2, r), V2 = simt::funnel_r(a2, a3, r);
-      uint32_t u = 0, nlit = 0, lits = 0, e;
-      // literals: up to 4, as long as the next one starts in the first 32 bits
-      for (;;) {
-        const uint32_t x = simt::funnel_r(V0, V1, u);
-        e = lit[x & (kLitRoot - 1)];
-        if (e & kNotLit) {
-          if ((e & kNotLit) != kLitSub) break;
-          e = lit[kLitRoot + (e & 0x1FFu) + ((x >> kLitRootBits) & ((1u << ((e >> 11) & 15u)) - 1u))];
-          if (e & kNotLit) break;
-        }
-        lits = simt::byte_perm(lits, e, 0x4321);
-        nlit++;
-        u += e >> 11;
-        if (nlit == 4u || u >= 32u) { e = 0u; break; }
-      }
-      uint32_t w0 = nlit << 24, used = u;
-      bool     odd = false;
-      if (e & kLitIsLen) {
-        if (u >= 32u) { V0 = V1; V1 = V2; V2 = 0u; }       // the funnel shifts below take u mod 32
-        const uint32_t M0 = simt::funnel_r(V0, V1, u), M1 = simt::funnel_r(V1, V2, u);
-        const uint32_t cl = (e >> 11) & 15u, xb = (e >> 8) & 7u;
-        const uint32_t len  = (e & 255u) + simt::bfe(M0, cl, xb) + 3u;
-        const uint32_t use1 = cl + xb;
-        const uint32_t D    = simt::funnel_r(M0, M1, use1);
-        uint32_t x = dist[D & (kDistRoot - 1)];
-        if (x & kDistSub)
-          x = dist[kDistRoot + (x & 0x1FFu) + ((D >> kDistRootBits) & ((1u << ((x >> 11) & 15u)) - 1u))];
-        const uint32_t dcl = (x >> 11) & 15u, dxb = (x >> 7) & 15u;
-        const uint32_t d1  = ((x & 3u) << dxb) + simt::bfe(D, dcl, dxb);
-        odd  = x == 0u;
-        w0  |= (d1 << 9) | len;
-        used = u + use1 + dcl + dxb;
-      } else if (e != 0u) {
-        odd = true;                                        // end of block, or no code here
-      }
-      if (odd) {
-        // the literals in front of the odd symbol are good; the careful step below deals with the symbol
-        if (nlit) { *tp++ = make_uint2(nlit << 24, lits); r += u; }
+      // -- every fourth trip
+      rg.topup(r);
+      // a lane below met the end of the block (or something that is no code): most likely everything from
+      // here on is not part of the block.  Stop as if the token segment was full; if that lane turns out to
+      // have been off the true trajectory, the next window simply starts here.
+      if (lane > *reinterpret_cast<volatile uint32_t*>(stop_lane) || ti + 4u > kSpecCap) {
+        if (!keep) { r0 = start; r = start; }
+        stat = LS_FULL;
         break;
       }
-      *tp++ = make_uint2(w0, lits);
-      r += used;
+      if ((trips4 & 3u) == 0u && ncp < kCpMax) cps[ncp++] = r | (ti << 20);
+      trips4++;
+      bool odd = false;
+#pragma unroll 1
+      for (int j = 0; j < 4 && r < fast_limit; j++) {
+        if (!keep && r >= start) { keep = 1u; r0 = r; }       // the warm-up ends on this token boundary
+        const uint32_t* p = rg.ring + ((r >> 5) & 31u);
+        const uint32_t a0 = p[0], a1 = p[1], a2 = p[2], a3 = p[3];
+        uint32_t V0 = simt::funnel_r(a0, a1, r), V1 = simt::funnel_r(a1, a2, r), V2 = simt::funnel_r(a2, a3, r);
+        uint32_t u = 0, nlit = 0, lits = 0, e = 0, x = V0;
+        // literals: up to 4, as long as the next one starts in the first 32 bits.  Four steps without a branch:
+        // every lane looks up all four, a lane that has met its first non-literal (kept in e) only stops taking
+        // them.  (Lanes differ in how many literals they have; a loop would run as long as the longest.)
+        bool go = true, more = false;
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+          const uint32_t ek  = lit[x & (kLitRoot - 1)];
+          const bool     isl = (ek & kNotLit) == 0u;
+          if (go && !isl) { e = ek; more = (ek & kNotLit) == kLitSub; }
+          const bool take = go && isl;
+          lits = take ? simt::byte_perm(lits, ek, DEFL_LIT_SEL(k)) : lits;
+          nlit = take ? (uint32_t)k + 1u : nlit;
+          u   += take ? ek >> 11 : 0u;
+          go   = take && u < 32u;
+          x = simt::funnel_r(V0, V1, u);
+        }
+        if (more) {
+          // a code longer than the root table's index: the same steps, rolled, with the second-level lookup
+#pragma unroll 1
+          for (;;) {
+            if ((e & kNotLit) == kLitSub)
+              e = lit[kLitRoot + (e & 0x1FFu) + ((x >> kLitRootBits) & ((1u << ((e >> 11) & 15u)) - 1u))];
+            if (e & kNotLit) break;
+            lits |= (e & 255u) << (8u * nlit);
+            nlit++;
+            u += e >> 11;
+            if (nlit == 4u || u >= 32u) { e = 0u; break; }
+            x = simt::funnel_r(V0, V1, u);
+            e = lit[x & (kLitRoot - 1)];
+          }
+        }
+        uint32_t w0 = nlit << 24, used = u;
+        if (e & kLitIsLen) {
+          if (u >= 32u) { V0 = V1; V1 = V2; V2 = 0u; }       // the funnel shifts below take u mod 32
+          const uint32_t M0 = simt::funnel_r(V0, V1, u), M1 = simt::funnel_r(V1, V2, u);
+          const uint32_t cl = (e >> 11) & 15u, xb = (e >> 8) & 7u;
+          const uint32_t len  = (e & 255u) + simt::bfe(M0, cl, xb) + 3u;
+          const uint32_t use1 = cl + xb;
+          const uint32_t D    = simt::funnel_r(M0, M1, use1);
+          uint32_t xd = dist[D & (kDistRoot - 1)];
+          if (xd & kDistSub)
+            xd = dist[kDistRoot + (xd & 0x1FFu) + ((D >> kDistRootBits) & ((1u << ((xd >> 11) & 15u)) - 1u))];
+          const uint32_t dcl = (xd >> 11) & 15u, dxb = (xd >> 7) & 15u;
+          const uint32_t d1  = ((xd & 3u) << dxb) + simt::bfe(D, dcl, dxb);
+          odd  = xd == 0u;
+          w0  |= (d1 << 9) | len;
+          used = u + use1 + dcl + dxb;
+        } else if (e != 0u) {
+          odd = true;                                        // end of block, or no code here
+        }
+        if (odd) {
+          // the literals in front of the odd symbol are good; the careful step below deals with the symbol
+          if (nlit) { if (keep) seg[ti] = make_uint2(nlit << 24, lits); ti += keep; r += u; }
+          break;
+        }
+        if (keep) seg[ti] = make_uint2(w0, lits);
+        ti += keep;
+        r += used;
+      }
+      if (odd) break;
     }
     // ---- one careful step: the ends of the sub-sequence, the input and the block, failures
-    if (r >= limit) break;
-    if (r >= next_cp) {
-      if (next_cp == start) { tp = seg; r0 = r; }
-      *cpp++ = (r - next_cp) | ((uint32_t)(tp - seg) << 8);
-      next_cp += kCpBits;
-    }
-    if (tp == tend) {
-      if (next_cp != start) { stat = LS_FULL; break; }
-      tp = seg;
-    }
+    if (r >= limit || stat != LS_OK) break;
+    if (!keep && r >= start) { keep = 1u; r0 = r; }
+    if (ti == kSpecCap) { stat = LS_FULL; break; }
     SubReader br;
     br.w = in.words; br.wend = in.wend;
     br.seek(bw, r);
     uint2    tok;
     uint32_t used, extra;
     const uint32_t s = careful_token(lit, dist, br, endr > r ? endr - r : 0u, tok, used, extra);
-    if (s != LS_OK && r < start) {
+    if (s != LS_OK && !keep) {
       // the warm-up ran into something that is not a token: start blind at `start`, as without a warm-up
       r = start;
       rg.drain();
       rg.init(ring_lane, in, base_quad, r);
-      it = 0;
       continue;
     }
-    if (s == LS_OK || tok_nlit(tok.x) != 0u) { *tp++ = tok; r += used; }
+    if (s == LS_OK || tok_nlit(tok.x) != 0u) { if (keep) seg[ti] = tok; ti += keep; r += used; }
     if (s != LS_OK) {
       stat = s;
       if (s == LS_EOB) r += extra;
@@ -283,9 +318,9 @@ DEFL_DEV void lane_spec4(const uint16_t* lit, const uint16_t* dist, const Input4
     }
   }
   rg.drain();
-  const uint32_t t = (uint32_t)(tp - seg);
-  tj.land = r; tj.stat = stat; tj.n = t; tj.m = 0; tj.nf = 0; tj.T = r0; tj.ncp = (uint32_t)(cpp - cps);
-  tj.s_land = r; tj.s_stat = stat; tj.s_n = t;
+  if (stat == LS_EOB || (stat & 0xFFu) == LS_FAIL) simt::atomic_min_shared(stop_lane, lane);
+  tj.land = r; tj.stat = stat; tj.n = ti; tj.m = 0; tj.nf = 0; tj.T = r0; tj.ncp = ncp;
+  tj.s_land = r; tj.s_stat = stat; tj.s_n = ti;
 }
 
 // fix-up pass: decode from the true start `T` until the speculative trajectory is met at a checkpoint
@@ -294,20 +329,18 @@ DEFL_DEV void lane_redo4(const uint16_t* lit, const uint16_t* dist, const Input4
   SubReader br;
   br.w = in.words; br.wend = in.wend;
   br.seek(bw, T);
-  uint32_t r = T, f = 0;
-  uint32_t k = (T - start + kCpBits - 1u) / kCpBits;
+  uint32_t r = T, f = 0, k = 0;
   const uint32_t ncp = tj.ncp;
-  uint32_t c = k < ncp ? cps[k] : 0u;
-  uint32_t target = k < ncp ? start + k * kCpBits + (c & 255u) : 0xFFFFFFFFu;
+  uint32_t c = k < ncp ? cps[k] : 0xFFFFFFFFu;
   tj.T = T;
   for (;;) {
-    while (r > target) {
+    // (checkpoints taken during the warm-up lie below `start` <= T and are skipped like any other)
+    while (k < ncp && (c & 0xFFFFFu) < r) {
       k++;
-      c = k < ncp ? cps[k] : 0u;
-      target = k < ncp ? start + k * kCpBits + (c & 255u) : 0xFFFFFFFFu;
+      c = k < ncp ? cps[k] : 0xFFFFFFFFu;
     }
-    if (r == target) {            // met the speculative trajectory: its tokens from c >> 8 on are true
-      tj.m = c >> 8; tj.nf = f;
+    if (k < ncp && (c & 0xFFFFFu) == r) {    // met the speculative trajectory: its tokens from c >> 20 on are true
+      tj.m = c >> 20; tj.nf = f;
       tj.land = tj.s_land; tj.stat = tj.s_stat; tj.n = tj.s_n;
       return;
     }
@@ -329,7 +362,6 @@ DEFL_DEV void lane_redo4(const uint16_t* lit, const uint16_t* dist, const Input4
     return;
   }
 }
-
 
 // ---- output side: the stage, its way to dst, Adler-32 ---------------------------------------------------------
 // The stage holds output positions [S0, P): what is not in dst yet (F..P, less than 16 bytes after every
@@ -449,7 +481,7 @@ DEFL_DEV uint32_t resolve4(WarpSmem4& sm, int lane, Out4& o, const uint2* toks, 
 
     uint32_t       len = tok_len(tok.x), nlit = tok_nlit(tok.x);
     const uint32_t d1 = tok_d1(tok.x);
-    const uint32_t lw = nlit ? tok.y >> (32u - 8u * nlit) : 0u;       // literal j in bits 8j..8j+7
+    const uint32_t lw = tok.y;                                         // literal j in bits 8j..8j+7
     uint32_t       olen = len + nlit;
     uint32_t       inc = olen;                                         // inclusive prefix sum of output lengths
 #pragma unroll
@@ -486,30 +518,42 @@ DEFL_DEV uint32_t resolve4(WarpSmem4& sm, int lane, Out4& o, const uint2* toks, 
     if ((uint32_t)lane >= n) { len = 0u; nlit = 0u; olen = 0u; }
     const uint32_t B = n ? simt::shfl(kFull, inc, (int)n - 1) : 0u;
 
-    // ---- literals: straight from the token
-    const uint32_t qs = o.P + ob - o.S0;                               // stage index of the token's first byte
-    if (nlit > 0u) st[qs] = (uint8_t)lw;
-    if (nlit > 1u) st[qs + 1u] = (uint8_t)(lw >> 8);
-    if (nlit > 2u) st[qs + 2u] = (uint8_t)(lw >> 16);
-    if (nlit > 3u) st[qs + 3u] = (uint8_t)(lw >> 24);
-
-    // ---- matches, in rounds: a token is copied once its source is final
-    const uint32_t mp = o.P + ob + nlit;                               // where the match goes
-    const uint32_t sp = mp - d1 - 1u;                                  // where it comes from
-    const bool has        = len != 0u;
-    const bool from_stage = sp >= o.V;
-    const bool from_dst   = sp + len <= o.F;
-    const bool slow       = has && (d1 + 1u < len || !(from_stage || from_dst) || len > 64u);
-    unsigned   pend = simt::ballot(kFull, has);
+    // ---- the batch's bytes -> stage.  A token's bytes (its literals, then its match) are assembled in
+    // registers as the aligned words they occupy in the stage and stored as whole words.  A word that two
+    // tokens share is written by the earlier one, which takes the later one's head bytes by shuffle when both
+    // are copied in the same round, and from the stage otherwise (then nobody else writes it in this round).
+    // Rounds: a token is copied once its source is final (most batches take one round).
+    const uint32_t ts = o.P + ob;                                      // where the token's bytes go
+    const uint32_t mp = ts + nlit;                                     // ... its match
+    const uint32_t sp = mp - d1 - 1u;                                  // where the match comes from
+    const uint32_t q  = ts - o.S0;                                     // stage index of the token's first byte
+    const uint32_t a  = q & 3u;
+    const uint32_t ms = a + nlit;                                      // the match's first byte in the token's word frame
+    const uint32_t e_ = (a + olen) & 3u;
+    const uint32_t klast = (a + olen + 3u) / 4u - 1u;                  // last word of the token (olen > 0)
+    const bool from_stage = sp >= o.V && sp - o.S0 >= 8u;
+    const bool from_dst   = sp + len <= o.F && sp >= 16u;
+    const bool fast = len == 0u || (len <= 16u && d1 + 1u >= len && (from_stage || from_dst));
+    unsigned   pend = simt::ballot(kFull, olen != 0u);
+    uint32_t* const stw = reinterpret_cast<uint32_t*>(st);
     simt::syncwarp(kFull);
 #pragma unroll 1
     while (pend) {
-      const int first = simt::ffs(pend) - 1;
-      if (simt::shfl(kFull, (uint32_t)slow, first)) {
-        // overlapping, long or straddling the stage's lower end: the whole warp, one byte per lane and step
+      const int      first = simt::ffs(pend) - 1;
+      const uint32_t done  = simt::shfl(kFull, ts, first);            // everything below is final
+      const bool     ready = ((pend >> lane) & 1u) && fast && (len == 0u || !from_stage || sp + len <= done);
+      const unsigned rm    = simt::ballot(kFull, ready);
+      if (!((rm >> first) & 1u)) {
+        // the first pending token is overlapping, long, straddles the stage's lower end or reads its own
+        // literals: the whole warp copies it, one byte per lane and step
         const uint32_t tx   = simt::shfl(kFull, tok.x, first);
-        const uint32_t mp0  = simt::shfl(kFull, mp, first);
-        const uint32_t len0 = tok_len(tx), dist0 = tok_d1(tx) + 1u;
+        const uint32_t lw0  = simt::shfl(kFull, lw, first);
+        const uint32_t nl0  = simt::shfl(kFull, nlit, first);
+        const uint32_t ts0  = done;
+        const uint32_t len0 = simt::shfl(kFull, len, first), dist0 = tok_d1(tx) + 1u;
+        if ((uint32_t)lane < nl0) st[ts0 - o.S0 + lane] = (uint8_t)(lw0 >> (8u * lane));
+        simt::syncwarp(kFull);
+        const uint32_t mp0 = ts0 + nl0;
         for (uint32_t j = (uint32_t)lane; j < len0; j += 32u) {
           const uint32_t s = mp0 - dist0 + (dist0 < len0 ? j % dist0 : j);
           const uint32_t b = s >= o.V ? (uint32_t)st[s - o.S0] : simt::ld_out8(o.dst + s);
@@ -519,46 +563,67 @@ DEFL_DEV uint32_t resolve4(WarpSmem4& sm, int lane, Out4& o, const uint2* toks, 
         simt::syncwarp(kFull);
         continue;
       }
-      const uint32_t done  = simt::shfl(kFull, mp, first);            // everything below is final
-      const bool     ready = ((pend >> lane) & 1u) && !slow && (!from_stage || sp + len <= done);
+      uint32_t D[6];
+#pragma unroll
+      for (int k = 0; k < 6; k++) D[k] = 0u;
       if (ready) {
-        const uint32_t qm = mp - o.S0;
-#pragma unroll 1
-        for (uint32_t c = 0; c < len; c += 16u) {
-          const uint32_t nb = len - c < 16u ? len - c : 16u;
-          uint32_t w[5];
-          uint32_t sh;
+        const uint64_t L64 = (uint64_t)lw << (8u * a);
+        D[0] = (uint32_t)L64; D[1] = (uint32_t)(L64 >> 32);
+        if (len) {
+          uint32_t w[7];
+          uint32_t sh, wl;
           if (from_stage) {
-            const uint32_t a = sp + c - o.S0;
-            const uint32_t* wp = reinterpret_cast<const uint32_t*>(st + (a & ~3u));
-            sh = (a & 3u) * 8u;
-            const uint32_t last = ((a & 3u) + nb - 1u) >> 2;
+            const uint32_t idx = sp - o.S0 - ms;                       // >= 1
+            const uint32_t* wp = stw + (idx >> 2);
+            sh = (idx & 3u) * 8u;
+            wl = ((idx & 3u) + ms + len - 1u) >> 2;                    // the word that holds the last source byte
 #pragma unroll
-            for (uint32_t i = 0; i < 5; i++) w[i] = i <= last ? wp[i] : 0u;
+            for (uint32_t k = 0; k < 7; k++) w[k] = k <= wl ? wp[k] : 0u;
           } else {
-            const uintptr_t a = (uintptr_t)(o.dst + sp + c);
-            const uint32_t* wp = reinterpret_cast<const uint32_t*>(a & ~(uintptr_t)3);
-            sh = (uint32_t)(a & 3u) * 8u;
-            const uint32_t last = ((uint32_t)(a & 3u) + nb - 1u) >> 2;
+            const uintptr_t ad = (uintptr_t)(o.dst + sp) - ms;
+            const uint32_t* wp = reinterpret_cast<const uint32_t*>(ad & ~(uintptr_t)3);
+            sh = (uint32_t)(ad & 3u) * 8u;
+            wl = ((uint32_t)(ad & 3u) + ms + len - 1u) >> 2;
 #pragma unroll
-            for (uint32_t i = 0; i < 5; i++) w[i] = i <= last ? simt::ld_outw(wp + i) : 0u;
+            for (uint32_t k = 0; k < 7; k++) w[k] = k <= wl ? simt::ld_outw(wp + k) : 0u;
           }
+          const uint64_t M64 = ~0ull << (8u * ms);                     // bytes of words 0, 1 that belong to the match
+          const uint32_t m0 = (uint32_t)M64, m1 = (uint32_t)(M64 >> 32);
+          D[0] = (simt::funnel_r(w[0], w[1], sh) & m0) | (D[0] & ~m0);
+          D[1] = (simt::funnel_r(w[1], w[2], sh) & m1) | (D[1] & ~m1);
 #pragma unroll
-          for (uint32_t wi = 0; wi < 4; wi++) {
-            const uint32_t v = simt::funnel_r(w[wi], w[wi + 1], sh);
+          for (int k = 2; k < 6; k++) D[k] = simt::funnel_r(w[k], w[k + 1], sh);
+        }
+      }
+      // the later neighbour's head bytes (its word 0 is this token's last word when e_ != 0)
+      const uint32_t nextD0 = simt::shfl(kFull, D[0], (lane + 1) & 31);
+      if (ready) {
+        uint32_t* const qw = stw + (q >> 2);
+        const bool prev_act = lane > 0 && ((rm >> (lane - 1)) & 1u);
+        const bool next_act = lane < 31 && ((rm >> (lane + 1)) & 1u);
+        uint32_t k0 = 0u;
+        if (a != 0u) {
+          if (prev_act) k0 = 1u;                                       // the earlier token writes that word
+          else { const uint32_t lo = (1u << (8u * a)) - 1u; D[0] = (D[0] & ~lo) | (qw[0] & lo); }
+        }
+        uint32_t tail = 0u;
+        const uint32_t keepm = e_ ? (1u << (8u * e_)) - 1u : 0xFFFFFFFFu;   // this token's bytes in its last word
+        if (e_ != 0u) tail = next_act ? nextD0 : qw[klast];
 #pragma unroll
-            for (uint32_t i = 0; i < 4; i++)
-              if (wi * 4u + i < nb) st[qm + c + wi * 4u + i] = (uint8_t)(v >> (8u * i));
+        for (uint32_t k = 0; k < 6; k++) {
+          if (k >= k0 && k <= klast) {
+            uint32_t v = D[k];
+            if (k == klast) v = (v & keepm) | (tail & ~keepm);
+            qw[k] = v;
           }
         }
       }
-      pend &= ~simt::ballot(kFull, ready);
+      pend &= ~rm;
       simt::syncwarp(kFull);
     }
-
     // ---- the stage's whole 16-byte groups go to dst
     o.P += B;
-    flush_groups(st, lane, o, o.P);
+    if (o.P - o.F >= 512u) flush_groups(st, lane, o, o.P);           // a full trip of 16-byte stores for every lane
     h += n;
     if (reason != R_NONE) return reason;
     if (short_batch) nxt = h + (uint32_t)lane < count ? simt::ld_tok2(toks + h + lane) : make_uint2(0u, 0u);
@@ -600,15 +665,16 @@ DEFL_DEV uint32_t decode_window4(WarpSmem4& sm, const WarpScratch4& sc, int lane
   const bool     active = start < endr || lane == 0;
   uint2*    seg = sc.spec + (uint32_t)lane * kSpecCap;
   uint2*    fix = sc.fix + (uint32_t)lane * kFixCap;
-  uint32_t* cps = sc.cps + (uint32_t)lane * kCpPerLane;
+  uint32_t* cps = sc.cps + (uint32_t)lane * kCpMax;
 
   LaneTraj tj;
   tj.land = start; tj.stat = LS_NONE; tj.n = 0; tj.m = 0; tj.nf = 0; tj.T = start; tj.ncp = 0;
   tj.s_land = start; tj.s_stat = LS_NONE; tj.s_n = 0;
   const uint32_t warm = (lane >= 1 && active) ? (warm_bits < S ? warm_bits : S) : 0u;   // lane 0 starts on a known boundary
+  if (lane == 0) sm.stop_lane = 32u;
   simt::syncwarp(kFull);                                                // the stage is the lanes' input rings now
   if (active) lane_spec4(sm.lit, sm.dist, in, base_quad, bw, start, limit, endr, seg, cps, tj, warm,
-                         sm.ring + lane * kRingWords);
+                         sm.ring + lane * kRingWords, &sm.stop_lane, (uint32_t)lane);
   simt::syncwarp(kFull);
 
   // fix-up rounds until every lane starts where its predecessor ended

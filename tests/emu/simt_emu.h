@@ -166,5 +166,9 @@ inline void cp_async16_n(void* smem_dst, const void* gsrc, uint32_t nbytes) {
   if (nbytes) memcpy(smem_dst, gsrc, nbytes > 16 ? 16 : nbytes);
 }
 inline uint4 ld_out128(const uint4* p) { uint4 r; memcpy(&r, p, 16); return r; }
+inline void atomic_min_shared(uint32_t* p, uint32_t v) {
+  uint32_t o = __atomic_load_n(p, __ATOMIC_RELAXED);
+  while (v < o && !__atomic_compare_exchange_n(p, &o, v, false, __ATOMIC_RELAXED, __ATOMIC_RELAXED)) {}
+}
 
 }  // namespace simt

@@ -28,7 +28,7 @@ class StreamOut(ctypes.Structure):
 def emu():
     srcs = [os.path.join(EMU_DIR, "emu_main.cpp"), os.path.join(EMU_DIR, "simt_emu.h"), CORE,
             os.path.join(CSRC, "pipeline.cuh"), os.path.join(CSRC, "warp_decode.cuh"),
-            os.path.join(CSRC, "split_decode.cuh")]
+            os.path.join(CSRC, "warp_decode4.cuh"), os.path.join(CSRC, "split_decode.cuh")]
     if not os.path.exists(EMU_SO) or any(os.path.getmtime(s) > os.path.getmtime(EMU_SO) for s in srcs):
         subprocess.check_call(["g++", "-std=c++17", "-O1", "-fPIC", "-shared", "-pthread", "-w",
                                "-o", EMU_SO, srcs[0]])
@@ -219,3 +219,43 @@ def test_split_mid_block_fixed_logic(emu):
         assert (end_bit.value + 7) // 8 == len(z) - 4
         assert ncand.value >= 4 and nchain.value >= ncand.value // 2, (kind, ncand.value, nchain.value)
     assert emu.emu_split_replayed() > before
+
+
+# ---- the v4 warp decoder (defl_b200/csrc/warp_decode4.cuh): one emulated warp ------------------------------
+def run_warp4(emu, data, cap, flags, mis=0, dmis=0):
+    buf = ctypes.create_string_buffer(len(data) + 32)
+    base = ctypes.addressof(buf)
+    off = (-base) % 16 + mis
+    ctypes.memmove(base + off, data, len(data))
+    dst = ctypes.create_string_buffer(cap + 64)
+    dbase = ctypes.addressof(dst)
+    doff = (-dbase) % 16 + dmis
+    o = StreamOut()
+    rc = emu.emu_warp4_inflate(ctypes.c_void_p(base + off), len(data), ctypes.c_void_p(dbase + doff), cap, flags,
+                               ctypes.byref(o))
+    return rc, dst.raw[doff: doff + o.outlen], o
+
+
+def test_warp4_corpus_and_mutants_logic(emu, corpus):
+    from test_oracle import _mutants
+    for i, e in enumerate(corpus):
+        rc0, out0, r0 = ol.port_inflate(e["data"], e["cap"], 0)
+        rc, out, o = run_warp4(emu, e["data"], e["cap"], 0, mis=i % 16, dmis=(i * 5) % 16)
+        assert same(rc, out, o, rc0, out0, r0), (e["name"], o.info >> 8)
+    for it, (d, cap, flags, raw, m) in enumerate(_mutants(9004, 250)):
+        rc0, out0, r0 = ol.port_inflate(d, cap, flags)
+        rc, out, o = run_warp4(emu, d, cap, flags, mis=it % 16, dmis=(it * 3) % 16)
+        assert same(rc, out, o, rc0, out0, r0), (it, m, o.info >> 8)
+
+
+def test_warp4_large_streams_logic(emu):
+    from defl_b200 import synth
+    specs = [("text", 200000, 1, 6, zlib.Z_DEFAULT_STRATEGY), ("log", 120000, 2, 9, zlib.Z_DEFAULT_STRATEGY),
+             ("png", 60000, 3, 1, zlib.Z_DEFAULT_STRATEGY), ("rand", 70000, 4, 6, zlib.Z_DEFAULT_STRATEGY),
+             ("zero", 300000, 5, 6, zlib.Z_DEFAULT_STRATEGY), ("text", 90000, 6, 6, zlib.Z_FIXED),
+             ("png", 40000, 8, 6, zlib.Z_HUFFMAN_ONLY)]
+    for k, (raw, z) in enumerate(synth.make_streams(specs, threads=1)):
+        rc0, out0, r0 = ol.port_inflate(z, len(raw), 1)
+        assert rc0 == 0 and out0 == raw
+        rc, out, o = run_warp4(emu, z, len(raw), 1, mis=(k * 5) % 16, dmis=(k * 7) % 16)
+        assert same(rc, out, o, rc0, out0, r0), (k, o.info >> 8)

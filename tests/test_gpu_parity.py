@@ -311,7 +311,7 @@ def test_pipeline_shapes(gpu_lib):
                 assert int(res[i]["adler"]) == (zlib.adler32(raw) & 0xFFFFFFFF)
     finally:
         d.set_pipeline_shape(0)
-        d.set_engine(4)
+        d.set_engine(3)
 
 
 def test_split_single_large_stream(gpu_lib):
@@ -474,3 +474,52 @@ def test_all_gpus_in_one_process(gpu_lib):
         for f in ("adler", "outlen", "inpos", "adler_stored"):
             assert int(a[f]) == int(b[f]), f
     assert torch.cuda.device_count() >= 1
+
+
+@pytest.mark.gpu
+def test_engine4_parity(gpu_lib, corpus, fuzz_ref):
+    """The v4 warp decoder (warp_decode4.cuh: literals+match tokens, shared-memory rings and stage; selectable,
+    not the default) against the same pins: the reference's corpus, its fuzzer verdicts, mutants vs the oracle
+    and every payload class at sizes with full 32-lane windows."""
+    from defl_b200 import synth
+    from test_oracle import _mutants
+    d = gpu_lib
+    try:
+        d.set_engine(4)
+        assert "engine=4" in d.engine_info()
+        datas = [e["data"] for e in corpus]
+        caps = [e["cap"] for e in corpus]
+        res, outs = d.infl_buf_batch(datas, caps, 0)
+        for e, g, out in zip(corpus, res, outs):
+            assert int(g["code"]) == e["ref_code"], (e["name"], int(g["info"]) >> 8)
+            if e["ref_code"] == 0:
+                assert int(g["outlen"]) == e["ref_outlen"] and int(g["inpos"]) == e["ref_inpos"], e["name"]
+                assert hashlib.sha256(bytes(out)).hexdigest() == e["ref_sha256"], e["name"]
+        fz = ol.RefFuzz(fuzz_ref["seed"])
+        n = 1000
+        cases = [fz.case(i) for i in range(n)]
+        fcaps = [max(fuzz_ref["outlens"][i] + 64, 4096) for i in range(n)]
+        res, outs = d.infl_buf_batch(cases, fcaps, 0)
+        for i in range(n):
+            if fuzz_ref["codes"][i] == 0:
+                assert int(res[i]["code"]) == 0 and int(res[i]["outlen"]) == fuzz_ref["outlens"][i], i
+                assert hashlib.sha256(bytes(outs[i])).hexdigest()[:16] == fuzz_ref["sha16"][i], i
+            else:
+                assert int(res[i]["code"]) != 0, i
+        for flags in (0, 1):
+            ms = [(dd, cap) for dd, cap, fl, raw, m in _mutants(2024, 1200) if fl == flags]
+            res, outs = d.infl_buf_batch([m[0] for m in ms], [m[1] for m in ms], flags)
+            _check_against_port(d, res, outs, [m[0] for m in ms], [m[1] for m in ms], flags, "engine4 mutants")
+        Z = zlib.Z_DEFAULT_STRATEGY
+        specs = [("text", 65536, 1, 6, Z), ("text", 900000, 2, 9, Z), ("log", 700000, 3, 6, Z), ("png", 400000, 4, 1, Z),
+                 ("rand", 300000, 5, 6, Z), ("zero", 2000000, 6, 6, Z), ("text", 500000, 7, 6, zlib.Z_FIXED),
+                 ("png", 300000, 8, 6, zlib.Z_HUFFMAN_ONLY), ("log", 400000, 9, 1, zlib.Z_RLE), ("text", 3, 10, 6, Z)]
+        streams = synth.make_streams(specs, threads=4)
+        res, outs = d.infl_buf_batch([z for _, z in streams], [len(r) for r, _ in streams],
+                                     d.INFL_ZLIB | d.INFL_BATCH_VERIFY_ADLER)
+        for (raw, z), g, out in zip(streams, res, outs):
+            assert int(g["code"]) == 0, int(g["info"]) >> 8
+            assert bytes(out) == raw and int(g["adler"]) == (zlib.adler32(raw) & 0xFFFFFFFF)
+            assert int(g["inpos"]) == len(z) - 4
+    finally:
+        d.set_engine(3)
