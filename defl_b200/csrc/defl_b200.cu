@@ -1357,9 +1357,29 @@ struct unz__stream_t {
   uint64_t total_in = 0;
   bool   any_piece = false;
 
-  // infl_stream() shim state
+  // infl_stream() state: the input so far (host copy + device copy), the output on the device, and -- on the
+  // device -- the last block boundary a call passed, from which the next call goes on (stream.c:468-794)
   std::vector<uint8_t> acc;       // accumulated compressed input
   bool                 strm_started = false;
+  DevBuf   sd_in, sd_out, sd_meta;   // meta: StreamResume + infl_batch_result_t
+  int      sd_dev = -1;              // device the three live on
+  size_t   uploaded = 0;             // bytes of acc that are in sd_in
+  size_t   tried_at = 0;             // acc.size() at the last decode attempt
+  uint32_t out_on_host = 0;          // dst[0, out_on_host) has been copied back
+  uint32_t last_feed = 0;            // size of the previous piece
+  bool     out_moved = false;        // infl_resize_output() gave a new dst since the last attempt
+  int      last_rc = UNZ_UNFINISHED; // what the last look said
+  ~unz__stream_t() {
+    if (sd_in.p || sd_out.p || sd_meta.p) {
+      int cur = 0;
+      cudaGetDevice(&cur);
+      if (sd_dev >= 0 && sd_dev != cur) cudaSetDevice(sd_dev);
+      if (sd_in.p) cudaFree(sd_in.p);
+      if (sd_out.p) cudaFree(sd_out.p);
+      if (sd_meta.p) cudaFree(sd_meta.p);
+      if (sd_dev >= 0 && sd_dev != cur) cudaSetDevice(cur);
+    }
+  }
 };
 
 namespace {
@@ -1379,12 +1399,86 @@ void stream_clear_pieces(unz__stream_t* s) {
 void stream_reset_state(unz__stream_t* s) {
   s->dstpos = 0; s->inpos = 0; s->adler = 1; s->adler_stored = 0; s->has_trailer = false;
   s->done = false; s->acc.clear(); s->strm_started = false;
+  s->uploaded = 0; s->tried_at = 0; s->out_on_host = 0; s->last_feed = 0; s->out_moved = false;
+  s->last_rc = UNZ_UNFINISHED;
+  if (s->sd_meta.p) {                       // forget the resume point (the device buffers are kept)
+    int cur = 0;
+    cudaGetDevice(&cur);
+    if (s->sd_dev >= 0 && s->sd_dev != cur) cudaSetDevice(s->sd_dev);
+    cudaMemset(s->sd_meta.p, 0, sizeof(defl::StreamResume));
+    if (s->sd_dev >= 0 && s->sd_dev != cur) cudaSetDevice(cur);
+  }
 }
 
 int decode_pieces(unz__stream_t* s, const infl_iovec_t* iov, size_t niov, infl_batch_result_t* r) {
   infl_batch_iov_item_t it;
   it.iov = iov; it.niov = niov; it.dst = s->dst; it.dstlen = s->dstlen;
   return infl_buf_batch_iov(&it, 1, s->flags == INFL_ZLIB ? INFL_ZLIB : 0, r);
+}
+
+// One look at a stream that arrives through infl_stream(): bring the new input to the device, decode from the
+// last block boundary an earlier look passed, bring the new output back.  Work per look: the new bytes plus one
+// block (the one the previous look ended in).
+int stream_attempt(unz__stream_t* s, infl_batch_result_t* r) {
+  Engine* E = nullptr;
+  if (engine_for_current_device(&E) != UNZ_OK) return UNZ_ERR;
+  std::lock_guard<std::mutex> g(E->mu);
+  cudaStream_t st = E->stream;
+  if (s->sd_dev >= 0 && s->sd_dev != E->dev) return fail("infl_stream: the handle was started on another device");
+  s->sd_dev = E->dev;
+  const size_t meta_bytes = sizeof(defl::StreamResume) + sizeof(infl_batch_result_t);
+  if (!s->sd_meta.p) {
+    if (s->sd_meta.reserve(256)) return UNZ_ERR;
+    CU_TRY(cudaMemsetAsync(s->sd_meta.p, 0, meta_bytes, st), "cudaMemsetAsync(stream state)");
+  }
+  auto* d_rs  = static_cast<defl::StreamResume*>(s->sd_meta.p);
+  auto* d_res = reinterpret_cast<infl_batch_result_t*>(static_cast<uint8_t*>(s->sd_meta.p) + sizeof(defl::StreamResume));
+  // input: only what is new, unless the buffer had to grow
+  const size_t n = s->acc.size();
+  if (n > 0xFFFFFFFFull) return fail("infl_stream: more than 4 GiB of input");
+  if (n > s->sd_in.cap) {
+    if (s->sd_in.p) { cudaStreamSynchronize(st); }
+    if (s->sd_in.reserve(std::max<size_t>(2 * n, 1 << 16))) return UNZ_ERR;
+    s->uploaded = 0;
+  }
+  if (n > s->uploaded)
+    CU_TRY(cudaMemcpyAsync(static_cast<uint8_t*>(s->sd_in.p) + s->uploaded, s->acc.data() + s->uploaded, n - s->uploaded,
+                           cudaMemcpyHostToDevice, st), "cudaMemcpyAsync H2D (infl_stream)");
+  s->uploaded = n;
+  // output: lives on the device; a larger or different caller buffer brings what it holds so far
+  const size_t want_out = std::max<size_t>(s->dstlen, 16);
+  if (want_out > s->sd_out.cap || s->out_moved) {
+    if (want_out > s->sd_out.cap) {
+      if (s->sd_out.p) cudaStreamSynchronize(st);
+      if (s->sd_out.reserve(want_out)) return UNZ_ERR;
+    }
+    if (s->out_on_host)
+      CU_TRY(cudaMemcpyAsync(s->sd_out.p, s->dst, s->out_on_host, cudaMemcpyHostToDevice, st), "cudaMemcpyAsync H2D (output so far)");
+    s->out_moved = false;
+  }
+  if (E->d_ws.reserve_exact(warp_kernel_workspace(E->sms))) return UNZ_ERR;
+  static bool attr_done[kMaxDevices] = {false};
+  if (!attr_done[E->dev]) {
+    CU_TRY(cudaFuncSetAttribute(defl::inflate_resume_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                (int)sizeof(defl::WarpSmem)), "cudaFuncSetAttribute(smem)");
+    attr_done[E->dev] = true;
+  }
+  defl::inflate_resume_kernel<<<1, 32, sizeof(defl::WarpSmem), st>>>(
+      static_cast<const uint8_t*>(s->sd_in.p), (uint32_t)n, static_cast<uint8_t*>(s->sd_out.p), s->dstlen,
+      s->flags == INFL_ZLIB ? INFL_ZLIB : 0, d_rs, d_res, static_cast<unsigned char*>(E->d_ws.p) + kWsHeader);
+  CU_TRY(cudaGetLastError(), "inflate_resume_kernel launch");
+  g_launches.fetch_add(1, std::memory_order_relaxed);
+  CU_TRY(cudaMemcpyAsync(r, d_res, sizeof(*r), cudaMemcpyDeviceToHost, st), "cudaMemcpyAsync D2H (result)");
+  CU_TRY(cudaStreamSynchronize(st), "cudaStreamSynchronize (infl_stream)");
+  s->tried_at = n;
+  const uint32_t outlen = (uint32_t)std::min<uint64_t>(r->outlen, s->dstlen);
+  if (outlen > s->out_on_host) {
+    CU_TRY(cudaMemcpyAsync(s->dst + s->out_on_host, static_cast<uint8_t*>(s->sd_out.p) + s->out_on_host,
+                           outlen - s->out_on_host, cudaMemcpyDeviceToHost, st), "cudaMemcpyAsync D2H (output)");
+    CU_TRY(cudaStreamSynchronize(st), "cudaStreamSynchronize (infl_stream output)");
+    s->out_on_host = outlen;
+  }
+  return UNZ_OK;
 }
 
 }  // namespace
@@ -1417,6 +1511,7 @@ UNZ_EXPORT void infl_reset(infl_stream_t* s, void* dst, uint32_t dstlen, int fla
 
 UNZ_EXPORT int infl_resize_output(infl_stream_t* s, void* dst, uint32_t dstlen) {      // mem.c:277-288
   if (!s || !dst || dstlen < s->dstpos) return UNZ_ERR;
+  s->out_moved = s->out_moved || static_cast<uint8_t*>(dst) != s->dst;
   s->dst = static_cast<uint8_t*>(dst);
   s->dstlen = dstlen;
   return UNZ_OK;
@@ -1486,7 +1581,8 @@ UNZ_EXPORT uint32_t infl_adler32(const infl_stream_t* s, uint32_t* stored, int* 
 // infl_resize_output() decodes again into the larger buffer.  See INTEGRATION.md.
 UNZ_EXPORT int infl_stream(infl_stream_t* s, const void* src, uint32_t srclen) {
   if (!s) return UNZ_ERR;
-  if (src && srclen) {
+  const bool poll = !(src && srclen);
+  if (!poll) {
     const uint8_t* p = static_cast<const uint8_t*>(src);
     s->acc.insert(s->acc.end(), p, p + srclen);
     s->strm_started = true;
@@ -1497,21 +1593,33 @@ UNZ_EXPORT int infl_stream(infl_stream_t* s, const void* src, uint32_t srclen) {
   if (s->acc.empty()) return UNZ_NOOP;
   if (s->flags == INFL_ZLIB && s->acc.size() < 2) return UNZ_UNFINISHED;   // stream.c:576-579
 
-  infl_iovec_t        iov{s->acc.data(), s->acc.size()};
+  // When to look: a decode attempt is a kernel launch and two small copies, so a caller that feeds single bytes
+  // must not pay for one per call.  Look when the caller polls (NULL, 0), while the stream is small, when it has
+  // grown by a sixteenth since the last look, or when this piece is shorter than the one before (the last piece
+  // of a file usually is).  Otherwise the answer is "go on": UNZ_UNFINISHED, as the reference gives for input
+  // that ends inside a block (stream.c:614-616).
+  const bool shorter = !poll && srclen < s->last_feed;
+  if (!poll) s->last_feed = srclen;
+  if (!(poll || s->acc.size() <= 512 || shorter || s->acc.size() - s->tried_at >= (s->tried_at >> 4) + 1)) return UNZ_UNFINISHED;
+  if (poll && s->tried_at == s->acc.size() && !s->out_moved) {
+    // nothing new since the last look: the same verdict without a launch
+    return s->last_rc;
+  }
   infl_batch_result_t r;
-  if (decode_pieces(s, &iov, 1, &r) != UNZ_OK) return UNZ_ERR;
+  if (stream_attempt(s, &r) != UNZ_OK) return UNZ_ERR;
   const uint32_t reason = (r.info >> INFL_INFO_REASON_SHIFT) & 0xFF;
+  s->dstpos = (uint32_t)r.outlen;
   if (r.code == UNZ_OK) {
-    s->dstpos = (uint32_t)r.outlen; s->inpos = (uint32_t)r.inpos;
+    s->inpos = (uint32_t)r.inpos;
     s->adler = r.adler; s->adler_stored = r.adler_stored;
     s->has_trailer = (r.info & INFL_INFO_HAS_TRAILER) != 0;
     s->done = true;
     return UNZ_OK;
   }
-  s->dstpos = (uint32_t)r.outlen;
-  if (reason == defl::R_TRUNCATED) return UNZ_UNFINISHED;   // stream.c:614-616 and friends
-  if (reason == defl::R_OUTPUT_FULL) return UNZ_EFULL;      // stream.c:625-627, :769-770
-  return UNZ_ERR;
+  s->last_rc = reason == defl::R_TRUNCATED ? UNZ_UNFINISHED      // stream.c:614-616 and friends
+             : reason == defl::R_OUTPUT_FULL ? UNZ_EFULL       // stream.c:625-627, :769-770
+                                             : UNZ_ERR;
+  return s->last_rc;
 }
 
 }  // extern "C"

@@ -169,6 +169,27 @@ inflate_warp4_kernel(const infl_batch_item_t* __restrict__ items, const uint32_t
   }
 }
 
+// infl_stream(): one stream whose input arrives in pieces, taken up at the last block boundary the previous call
+// passed (reference: the resumable state machine of src/infl/stream.c:468-794).  One warp; input and output stay
+// on the device between calls.
+__global__ void __launch_bounds__(32)
+inflate_resume_kernel(const uint8_t* __restrict__ src, uint32_t srclen, uint8_t* __restrict__ dst, uint32_t cap,
+                      int flags, StreamResume* __restrict__ rs, infl_batch_result_t* __restrict__ result,
+                      unsigned char* __restrict__ scratch) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  WarpSmem&         sm = *reinterpret_cast<WarpSmem*>(smem_raw);
+  const WarpScratch sc = scratch_of(scratch);
+  const int lane = threadIdx.x;
+  StreamOut o;
+  inflate_stream_warp(sm, sc, lane, src, srclen, dst, cap, flags, o, rs);
+  if (lane == 0) {
+    infl_batch_result_t r;
+    r.code = o.code; r.adler = o.adler; r.outlen = o.outlen; r.inpos = o.inpos;
+    r.adler_stored = o.adler_stored; r.info = o.info;
+    *result = r;
+  }
+}
+
 // K2: descriptor-driven gather of input pieces into contiguous device memory (replaces the
 // host-side join of infl_include, reference src/infl/mem.c:121-155, and the chunk walk of
 // REFILL, infl.c:1121-1128).  One warp per piece per trip; 16-byte stores when the

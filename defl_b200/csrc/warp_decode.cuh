@@ -689,16 +689,29 @@ DEFL_DEV uint32_t decode_window(WarpSmem& sm, const WarpScratch& sc, int lane, c
 }
 
 // ---- one stream, start to finish, by one warp ------------------------------------------------------------------
+// Where a decode that ran out of input (or output room) can be taken up again: the last block boundary it passed.
+// infl_stream() keeps one per handle on the device (reference: the saved state of stream.c:468-794).
+struct StreamResume {
+  uint64_t bit;      // bits consumed from src[0] up to that boundary
+  uint32_t pos;      // bytes produced up to it
+  uint32_t valid;    // 0: start at the stream's first byte
+};
+
 DEFL_DEV void inflate_stream_warp(WarpSmem& sm, const WarpScratch& sc, int lane, const uint8_t* src,
-                                  uint32_t srclen, uint8_t* dst, uint32_t cap, int flags, StreamOut& out) {
+                                  uint32_t srclen, uint8_t* dst, uint32_t cap, int flags, StreamOut& out,
+                                  StreamResume* rs = nullptr) {
   Lane<32> L;
   L.gmask = kFull; L.lane = lane; L.wlane = lane;
   out.code = -1; out.adler = 1; out.outlen = 0; out.inpos = 0; out.adler_stored = 0; out.info = 0;
   if (srclen == 0) { out.code = 0; return; }       // all pieces empty => UNZ_OK (infl.c:1547-1550)
 
   const bool zlib = (flags & 0xFF) == 1;
+  const bool resume = rs != nullptr && rs->valid != 0u;
+  const uint64_t rbit = resume ? rs->bit : 0u;
+  uint32_t   pos = resume ? rs->pos : 0u;
+  simt::syncwarp(kFull);                             // every lane has read *rs before lane 0 writes it again
   uint32_t   body = 0;
-  if (zlib) {
+  if (zlib && !resume) {
     const uint32_t hr = zlib_header(src, srclen, body);
     if (hr) { out.info = hr << 8; return; }
   }
@@ -708,9 +721,9 @@ DEFL_DEV void inflate_stream_warp(WarpSmem& sm, const WarpScratch& sc, int lane,
   BitReader br;
   br.w    = reinterpret_cast<const uint32_t*>((uintptr_t)src - mis);
   br.wend = (uint32_t)(((uint64_t)mis + srclen + 3u) >> 2);
-  br.seek(base_bit + body * 8u);
+  br.seek(resume ? base_bit + rbit : base_bit + body * 8u);
 
-  uint32_t pos = 0, reason = R_NONE;
+  uint32_t reason = R_NONE;
   bool     fixed_ready = false;
 #pragma unroll 1
   for (;;) {
@@ -740,6 +753,9 @@ DEFL_DEV void inflate_stream_warp(WarpSmem& sm, const WarpScratch& sc, int lane,
       br.seek(cur);
     }
     if (bfinal) break;
+    if (rs != nullptr && lane == 0) {                // a block boundary: a later call can go on from here
+      rs->bit = br.bitpos() - base_bit; rs->pos = pos; rs->valid = 1u;
+    }
   }
   if (reason) { out.info = reason << 8; out.outlen = pos; return; }
 
