@@ -48,10 +48,13 @@ def parse():
     ap.add_argument("--mixed-no-fixed", action="store_true", help="mixed workload without the forced Z_FIXED streams (diagnosis)")
     ap.add_argument("--mixed-unique-mib", type=int, default=1024, help="mixed workload: distinct MiB generated on the host")
     ap.add_argument("--chunk-streams", type=int, default=256, help="chunks workload: 4 MiB streams per step")
-    ap.add_argument("--workload", default="batch", choices=["batch", "single", "mixed", "chunks"],
+    ap.add_argument("--sharded-pool-mib", type=int, default=512, help="mixed_sharded sub-record: distinct MiB generated on the host")
+    ap.add_argument("--no-extra", action="store_true", help="headline only: skip the workloads sub-records")
+    ap.add_argument("--workload", default="batch", choices=["batch", "single", "mixed", "chunks", "sharded"],
                     help="batch = configs[1] (headline); single = configs[3], one large stream, split-point decode")
     ap.add_argument("--single-bytes", type=int, default=1 << 30)
     ap.add_argument("--e2e-steps", type=int, default=2)
+    ap.add_argument("--e2e-streams", type=int, default=50_000, help="streams per GPU in the end-to-end leg (the same at every N)")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--profile", action="store_true", help="short run for ncu: no e2e, no cpu baseline")
@@ -206,18 +209,21 @@ def run_reference_arm(args, rank, world):
         "cpu_baseline": {"value": val, "unit": UNIT, "cores": threads, "kind": kind, "sample": sample},
         "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
+        "same_config_note": "same stream shape as the GPU arm's config (64 KiB text streams, level 6); each step decodes a "
+                            f"{n}-stream sample of the 100 000, so GB/s compare per byte, ms_per_step do not",
     }))
 
 
-def run_single(args, d, dev):
+def run_single(args, d, dev, stream=None, what=None, steps=None):
     """BASELINE.json configs[3]: ONE zlib stream (default 1 GiB of text/log stripes), device resident, decoded by
     the split-point path.  Timed on the host around the whole call (it contains host-side steps: candidate
-    selection, the chunk chain), bracketed by device synchronisation."""
+    selection, the chunk chain), bracketed by device synchronisation.  -> the record (a JSON-able dict)."""
     import torch
     from defl_b200 import synth
     t0 = time.time()
-    raw, z = synth.single_stream(args.single_bytes, seed=7)
+    raw, z = stream if stream is not None else synth.single_stream(args.single_bytes, seed=7)
     gen_s = time.time() - t0
+    steps = steps or args.steps
     t_src = torch.frombuffer(bytearray(z), dtype=torch.uint8).to(dev)
     t_dst = torch.zeros(len(raw), dtype=torch.uint8, device=dev)
     items = np.zeros(1, dtype=d.ITEM_DTYPE)
@@ -225,12 +231,12 @@ def run_single(args, d, dev):
     results = np.zeros(1, dtype=d.RESULT_DTYPE)
     from defl_b200 import api
     flags = d.INFL_ZLIB | d.INFL_BATCH_VERIFY_ADLER | d.INFL_BATCH_DEVICE_PTRS
-    for _ in range(max(args.warmup, 1)):
+    for _ in range(max(min(args.warmup, 3), 1)):
         api.infl_buf_batch_raw(items, flags, results)
     torch.cuda.synchronize()
     l0 = d.kernel_launch_count()
     times = []
-    for _ in range(args.steps):
+    for _ in range(steps):
         t_dst.zero_()
         torch.cuda.synchronize()
         t0 = time.perf_counter()
@@ -243,23 +249,35 @@ def run_single(args, d, dev):
     split = bool(int(results["info"][0]) & 4)
     out = t_dst.cpu().numpy()
     assert out.tobytes() == raw, "single-stream output differs"
+    del out, t_dst, t_src
     ms = float(np.mean(times)) * 1e3
     peak, peak_src = peaks()
     achieved = (len(z) + len(raw)) / (ms / 1e3) / 1e9
-    print(json.dumps({
+    return {
         "metric": "decompressed GB/s, single zlib stream", "value": len(raw) / (ms / 1e3) / 1e9, "unit": UNIT, "n_gpus": 1,
-        "steps": args.steps, "warmup": max(args.warmup, 1), "ms_per_step": ms, "best_ms": min(times) * 1e3,
+        "steps": steps, "warmup": max(min(args.warmup, 3), 1), "ms_per_step": ms, "best_ms": min(times) * 1e3,
         "higher_is_better": True, "scaling": "replicas only", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-        "config": {"workload": "configs[3]: single deflate stream decoded with speculative intra-stream split points",
-                   "raw_bytes": len(raw), "compressed_bytes": len(z), "split_decode": split, "gen_seconds": round(gen_s, 1),
-                   "engine": d.engine_info()},
+        "byte_exact": True,
+        "config": {"workload": what or "configs[3]: single deflate stream decoded with speculative intra-stream split points",
+                   "raw_bytes": len(raw), "compressed_bytes": len(z), "ratio": len(raw) / len(z), "split_decode": split,
+                   "gen_seconds": round(gen_s, 1), "engine": d.engine_info()},
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                      "traffic": None, "peak_source": peak_src, "kernel": "split_chunk_kernel (count + decode passes), "
                      "find_block_starts_kernel, marker_resolve_kernel", "algorithmic_bytes_per_launch": len(z) + len(raw)},
-        "gpu_launches": int(launches)}))
+        "gpu_launches": int(launches)}
 
 
-def run_chunks(args, d, dev):
+def single_history_stream(total_bytes, seed=11, level=6):
+    """ONE deflate() history over `total_bytes` of `text` (no flush points, no history resets)."""
+    from defl_b200 import synth
+    stripe = 8 << 20
+    raw = b"".join(synth.payload("text", min(stripe, total_bytes - o), seed * 7919 + o // stripe)
+                   for o in range(0, total_bytes, stripe))
+    c = zlib.compressobj(level, zlib.DEFLATED, 15, 8, zlib.Z_DEFAULT_STRATEGY)
+    return raw, c.compress(raw) + c.flush()
+
+
+def run_chunks(args, d, dev, nstreams=None, steps=None):
     """BASELINE.json configs[2]: 4 MiB streams (png and text, level 6) handed over as lists of pieces, never joined
     on the host, through infl_buf_batch_iov (the batched infl_include).  Piece sizes follow SURVEY.md 8(d), driven by
     the LCG of test_fuzz.c:139-142: (ii) half 1-16 B / half 1-32768 B, (iii) 8193-32192 B, and (i) all 1-byte pieces
@@ -267,7 +285,7 @@ def run_chunks(args, d, dev):
     gather, the decode and D2H."""
     import torch
     from defl_b200 import synth, api
-    n = args.chunk_streams
+    n = nstreams or args.chunk_streams
     Z = zlib.Z_DEFAULT_STRATEGY
     t0 = time.time()
     streams = synth.make_streams([("png" if i & 1 else "text", 4 << 20, 500 + i, 6, Z) for i in range(n)],
@@ -330,16 +348,16 @@ def run_chunks(args, d, dev):
                 "h2d_bytes": int(sl[idx].sum()), "d2h_bytes": outb, "launches": int(launches)}
 
     allidx = np.arange(n)
-    steps = max(args.steps, 1)
+    steps = max(steps or args.steps, 1)
     mix = run("mix", allidx, steps)
     large = run("large", allidx, steps)
     one = run("one", allidx[:2], 1)
     peak, peak_src = peaks()
     achieved = (mix["h2d_bytes"] * 2 + mix["h2d_bytes"] + mix["d2h_bytes"]) / (mix["ms_per_step"] / 1e3) / 1e9
-    print(json.dumps({
+    return {
         "metric": "decompressed GB/s, zlib streams given as chunk lists, host to host", "value": mix["GBps"], "unit": UNIT,
         "n_gpus": 1, "steps": steps, "warmup": 1, "ms_per_step": mix["ms_per_step"], "higher_is_better": True,
-        "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+        "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic", "byte_exact": True,
         "config": {"workload": "configs[2]: 4 MiB streams (png / text, level 6) as lists of 1 B - 32 KiB pieces through "
                                "infl_buf_batch_iov; value = chunking (ii)", "chunking_ii_mix": mix, "chunking_iii_8k_32k": large,
                    "chunking_i_all_1_byte": one, "engine": d.engine_info(), "gen_seconds": round(gen_s, 1),
@@ -350,7 +368,125 @@ def run_chunks(args, d, dev):
         "cpu_baseline": None,
         "e2e": {"value": mix["GBps"], "unit": UNIT, "h2d_bytes_per_step": mix["h2d_bytes"] + 16 * mix["pieces_per_step"],
                 "d2h_bytes_per_step": mix["d2h_bytes"]},
-        "gpu_launches": mix["launches"] * steps}))
+        "gpu_launches": mix["launches"] * steps}
+
+
+def run_mixed_sharded(args, d, dev, rank, world, local, dist, per_gpu_gib=None, pool_mib=None, steps=None):
+    """BASELINE.json configs[4] as north_star states it: ONE mixed batch (one descriptor table, the same on every
+    rank: same seeds) cut into `world` byte-balanced shards by infl_batch_partition (greedy LPT on srclen + dstlen,
+    SURVEY.md 8e); rank r decodes the members with part_of == r from its own device memory, no collective on the
+    data path.  The table is a unique pool tiled to world x per_gpu_gib GiB of output (64 GiB at 8 GPUs), every
+    member in physically distinct memory.  -> the sub-record (rank 0), None elsewhere."""
+    import torch
+    from defl_b200 import synth, api
+    per_gpu_gib = per_gpu_gib or args.mixed_gib
+    pool_mib = pool_mib or args.sharded_pool_mib
+    steps = steps or max(2, min(args.steps, 3))
+    t0 = time.time()
+    specs = synth.config5_specs(pool_mib << 20, first_seed=0)            # every rank: the same pool
+    st = synth.make_streams(specs, threads=max(1, (os.cpu_count() or 1) // max(1, world)))
+    raws, zs = [r for r, _ in st], [z for _, z in st]
+    gen_s = time.time() - t0
+    unique = len(zs)
+    raw_len = np.array([len(r) for r in raws], dtype=np.int64)
+    z_len = np.array([len(z) for z in zs], dtype=np.int64)
+    pool_out = int(raw_len.sum())
+    reps = max(1, int(round(world * per_gpu_gib * (1 << 30) / pool_out)))
+    n = unique * reps
+    k = np.arange(n, dtype=np.int64)
+    tab_src_len, tab_dst_len = z_len[k % unique], raw_len[k % unique]     # THE table: member i = pool entry i % unique
+    part_of, load = api.batch_partition(tab_src_len, tab_dst_len, world)
+    mine = np.nonzero(part_of == rank)[0]
+    u_of = mine % unique
+    # this rank's shard, every member in its own memory
+    src_off = np.zeros(len(mine), dtype=np.int64)
+    at = 0
+    for j, u in enumerate(u_of):
+        src_off[j] = at
+        at = (at + int(z_len[u]) + 15) // 16 * 16
+    h_src = np.zeros(max(at, 16), dtype=np.uint8)
+    for j, u in enumerate(u_of):
+        h_src[src_off[j]: src_off[j] + z_len[u]] = np.frombuffer(zs[u], dtype=np.uint8)
+    t_src = torch.from_numpy(h_src).to(dev)
+    del h_src
+    dlen = raw_len[u_of]
+    dst_off = np.concatenate([[0], np.cumsum(dlen)])[:-1]
+    t_dst = torch.zeros(int(dlen.sum()) + 16, dtype=torch.uint8, device=dev)
+    items = np.zeros(len(mine), dtype=d.ITEM_DTYPE)
+    items["src"] = t_src.data_ptr() + src_off
+    items["srclen"] = z_len[u_of]
+    items["dst"] = t_dst.data_ptr() + dst_off
+    items["dstlen"] = dlen
+    results = np.zeros(len(mine), dtype=d.RESULT_DTYPE)
+    flags = d.INFL_ZLIB | d.INFL_BATCH_VERIFY_ADLER | d.INFL_BATCH_DEVICE_PTRS
+    in_bytes, out_bytes = int(z_len[u_of].sum()), int(dlen.sum())
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(2):
+        api.infl_buf_batch_raw(items, flags, results)
+    barrier()
+    l0 = d.kernel_launch_count()
+    times = []
+    for _ in range(steps):
+        barrier()
+        t = time.perf_counter()
+        api.infl_buf_batch_raw(items, flags, results)
+        torch.cuda.synchronize()
+        times.append(time.perf_counter() - t)
+    launches = d.kernel_launch_count() - l0
+    barrier()
+    # byte-exact: code, length and Adler-32 of every member (the stored Adler is zlib's own of the raw bytes); the
+    # first copy of every pool entry on this rank against the generator's bytes; every further copy against the first
+    assert (results["code"] == 0).all(), f"decode failed: {int((results['code'] != 0).sum())} streams"
+    assert (results["outlen"] == dlen.astype(np.uint64)).all() and (results["adler"] == results["adler_stored"]).all()
+    first = {}
+    for j, u in enumerate(u_of):
+        a, b = int(dst_off[j]), int(dst_off[j] + dlen[j])
+        if int(u) not in first:
+            first[int(u)] = (a, b)
+            assert t_dst[a:b].cpu().numpy().tobytes() == raws[int(u)], f"member {mine[j]} differs from the generator's bytes"
+        else:
+            fa, fb = first[int(u)]
+            assert torch.equal(t_dst[a:b], t_dst[fa:fb]), f"member {mine[j]} differs from its twin"
+    n_split = int(((results["info"] & 4) != 0).sum())
+    mean_ms = float(np.mean(times)) * 1e3
+    stat = torch.tensor([mean_ms, float(in_bytes + out_bytes), float(out_bytes), float(len(mine)), float(n_split)],
+                        dtype=torch.float64, device=dev)
+    if world > 1:
+        allst = [torch.zeros_like(stat) for _ in range(world)]
+        dist.all_gather(allst, stat)
+        allst = torch.stack(allst).cpu().numpy()
+    else:
+        allst = stat.cpu().numpy()[None, :]
+    del t_src, t_dst
+    torch.cuda.empty_cache()
+    if rank != 0:
+        return None
+    peak, peak_src = peaks()
+    shard_ms = [float(x) for x in allst[:, 0]]
+    tmax = max(shard_ms) / 1e3
+    alg = float(allst[:, 1].sum())
+    tot_out = float(allst[:, 2].sum())
+    return {
+        "metric": "decompressed GB/s, ONE mixed batch sharded by infl_batch_partition", "value": tot_out / tmax / 1e9,
+        "unit": UNIT, "n_gpus": world, "steps": steps, "ms_per_step": max(shard_ms), "byte_exact": True,
+        "shard_ms": shard_ms, "shard_ms_min": min(shard_ms), "shard_ms_max": max(shard_ms),
+        "shard_algorithmic_bytes": [float(x) for x in allst[:, 1]],
+        "byte_imbalance_max_over_mean": float(allst[:, 1].max() / allst[:, 1].mean()),
+        "roofline": {"bound": "hbm", "achieved": alg / tmax / 1e9, "peak": peak * world, "unit": "GB/s",
+                     "frac": alg / tmax / 1e9 / (peak * world), "peak_source": peak_src + f" x {world} GPUs",
+                     "algorithmic_bytes_per_step": alg},
+        "config": {"workload": "configs[4]: mixed batch (stored/fixed/dynamic, levels 1/6/9, 64 KiB-4 MiB), "
+                               f"{tot_out / 2**30:.1f} GiB out in one table of {n} members, LPT-sharded over {world} GPU(s)",
+                   "members": n, "members_per_shard": [int(x) for x in allst[:, 3]], "split_decoded": int(allst[:, 4].sum()),
+                   "unique_streams": unique, "unique_out_bytes": pool_out, "gen_seconds": round(gen_s, 1),
+                   "timing": "host clock around infl_buf_batch(INFL_BATCH_DEVICE_PTRS) per rank, device-synchronised; "
+                             "value = all bytes / slowest shard"},
+        "gpu_launches": int(launches)}
 
 
 def run_mixed(args, d, dev, rank, world, local, dist):
@@ -508,13 +644,21 @@ def main():
         d.set_engine(args.engine)
 
     if args.workload == "single":
-        run_single(args, d, dev)
+        print(json.dumps(run_single(args, d, dev)))
         return
     if args.workload == "mixed":
         run_mixed(args, d, dev, rank, world, local, dist)
         return
     if args.workload == "chunks":
-        run_chunks(args, d, dev)
+        print(json.dumps(run_chunks(args, d, dev)))
+        return
+    if args.workload == "sharded":
+        rec = run_mixed_sharded(args, d, dev, rank, world, local, dist)
+        if rank == 0:
+            print(json.dumps(rec))
+        if world > 1:
+            dist.barrier()
+            dist.destroy_process_group()
         return
 
     n = args.streams
@@ -597,16 +741,17 @@ def main():
         try:
             tj = json.load(open(prof))
             roofline["traffic"] = float(tj["dram_bytes_over_algorithmic_bytes"]) * (in_bytes + out_bytes)
-            roofline["traffic_source"] = "ncu dram bytes / algorithmic bytes = %.2f at 16000 streams per launch (%s), scaled to this launch" % (
-                tj["dram_bytes_over_algorithmic_bytes"], "profiles/r01_v3d_ncu_full_summary.json")
+            roofline["traffic_source"] = "ncu dram__bytes_read.sum + dram__bytes_write.sum over algorithmic bytes = %.2f (%s), times this launch's algorithmic bytes" % (
+                tj["dram_bytes_over_algorithmic_bytes"], tj.get("source", "profiles/traffic.json"))
         except Exception:
             pass
 
     # ---- end to end through the C ABI with host buffers ------------------------------------------
     e2e = None
     if not args.no_e2e:
-        # pinned host memory is per rank: keep the whole job's under ~20 GB (8 ranks x 9.5 GB would not be polite)
-        ne = n if world <= 2 else max(unique, min(n, 200_000 // world))
+        # the same job on every rank at every N (the curve compares like with like): 50 000 streams per GPU,
+        # 3.3 GB out + 1.5 GB in of pinned host memory per rank
+        ne = min(n, args.e2e_streams)
         h_src = torch.from_numpy(src_h).repeat((ne + unique - 1) // unique).pin_memory()
         h_dst = torch.zeros(ne * STREAM_BYTES, dtype=torch.uint8).pin_memory()
         items = np.zeros(ne, dtype=d.ITEM_DTYPE)
@@ -632,14 +777,56 @@ def main():
         tt = torch.tensor([dt], dtype=torch.float64, device=dev)
         if world > 1:
             dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        # the ceiling of this leg on this box: the same bytes, copies only (H2D of the compressed bytes and D2H of
+        # the decoded bytes on two streams at once, pinned memory, all ranks at the same time, nothing decoded)
+        c_in = torch.empty(e_in, dtype=torch.uint8, device=dev)
+        c_out = torch.empty(e_out, dtype=torch.uint8, device=dev)
+        s1, s2 = torch.cuda.Stream(), torch.cuda.Stream()
+        hs, hd = h_src[:e_in], h_dst[:e_out]
+
+        def copies():
+            with torch.cuda.stream(s1):
+                c_in.copy_(hs, non_blocking=True)
+            with torch.cuda.stream(s2):
+                hd.copy_(c_out, non_blocking=True)
+        copies()
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(args.e2e_steps):
+            copies()
+        torch.cuda.synchronize()
+        cdt = time.perf_counter() - t0
+        ct = torch.tensor([cdt], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(ct, op=dist.ReduceOp.MAX)
         e2e = {"value": e_out * world * args.e2e_steps / float(tt.item()) / 1e9, "unit": UNIT,
                "h2d_bytes_per_step": e_in + 36 * ne, "d2h_bytes_per_step": e_out + 32 * ne,
-               "steps": args.e2e_steps, "streams_per_gpu": ne, "api": "infl_buf_batch (host pointers, pinned)"}
-        del h_src, h_dst
+               "steps": args.e2e_steps, "streams_per_gpu": ne, "api": "infl_buf_batch (host pointers, pinned)",
+               "copy_ceiling": e_out * world * args.e2e_steps / float(ct.item()) / 1e9,
+               "copy_ceiling_what": "decoded GB/s if the step were only its pinned H2D + D2H copies (both directions at once, "
+                                    "all ranks together), measured right after the timed leg",
+               "of_copy_ceiling": float(ct.item()) / float(tt.item())}
+        del h_src, h_dst, c_in, c_out, hs, hd
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
         cpu, _ = cpu_reference_run(zs[: min(unique, 4096)])
+
+    # ---- the other north_star configs, as sub-records of the same line --------------------------------
+    workloads = None
+    if not args.profile and not args.no_extra and not args.lanes and args.engine in (0, 3):
+        del batch, t_src, t_dst, t_pool, tile0
+        torch.cuda.empty_cache()
+        workloads = {}
+        workloads["mixed_sharded"] = run_mixed_sharded(args, d, dev, rank, world, local, dist)
+        if world == 1:
+            workloads["single_1gib"] = run_single(args, d, dev, steps=3,
+                                                  what="configs[3]: one 1 GiB zlib stream of text/log stripes, built pigz-style "
+                                                       "(64 slices, each ending in a full flush: 63 history resets)")
+            workloads["single_1gib_one_history"] = run_single(
+                args, d, dev, stream=single_history_stream(1 << 30), steps=3,
+                what="configs[3]: one 1 GiB zlib stream of text from ONE deflate() history (level 6, no flush points)")
+            workloads["chunks"] = run_chunks(args, d, dev, nstreams=64, steps=2)
 
     if rank == 0:
         line = {
@@ -657,7 +844,7 @@ def main():
                        "parallelism": f"{world} x independent shards, no collective",
                        "engine": d.engine_info(), "gen_seconds": round(gen_s, 1)},
             "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches),
-            "clocks": sampler.summary(),
+            "clocks": sampler.summary(), "workloads": workloads,
         }
         print(json.dumps(line))
     if world > 1:

@@ -318,7 +318,7 @@ uint32_t env_u32(const char* name, uint32_t dflt, uint32_t lo, uint32_t hi) {
 std::atomic<uint64_t> g_split_decodes{0};
 
 struct SplitBufs {
-  DevBuf d_found, d_cand, d_jobs, d_outs, d_outs2, d_sym, d_off, d_partial, d_wbuf, d_tok, d_streams, d_peek, d_at;
+  DevBuf d_found, d_cand, d_jobs, d_outs, d_outs2, d_sym, d_off, d_partial, d_wbuf, d_wdbl, d_tok, d_streams, d_peek, d_at;
 };
 SplitBufs g_split[kMaxDevices];
 
@@ -633,10 +633,42 @@ int split_decode_many(Engine* E, const SplitInput* in, size_t nin, int flags, vo
   // ---- D: windows, then markers -> bytes + Adler-32 partial sums
   std::vector<uint32_t> partial((size_t)blk_total * 2);
   if (win_total) {
-    window_resolve_kernel<<<win_total * 16u, 256, 0, st>>>(d_sd, ns, static_cast<uint16_t*>(SB.d_sym.p),
-                                                           static_cast<uint64_t*>(SB.d_off.p), static_cast<uint8_t*>(SB.d_wbuf.p));
-    CU_TRY(cudaGetLastError(), "window_resolve_kernel launch");
-    g_launches.fetch_add(1, std::memory_order_relaxed);
+    // long chains of chunks (one history over hundreds of MB): pointer doubling over the windows; else every
+    // marker of a window is followed back directly (few hops)
+    uint32_t max_win = 0;
+    bool     frames_ok = true;
+    for (size_t p = 0, run = 0; p < chain.size(); p++) {
+      const bool first = p == 0 || chain[p - 1].stream != chain[p].stream;
+      const bool lastc = p + 1 == chain.size() || chain[p + 1].stream != chain[p].stream;
+      run = first ? 0 : run + 1;                              // index of the window before this chunk, + 1
+      max_win = std::max<uint32_t>(max_win, (uint32_t)run);
+      if (!first && !lastc && chain[p].bytes < kWinBytes) frames_ok = false;
+    }
+    const uint32_t dbl_from = env_u32("DEFL_SPLIT_DOUBLING_FROM", 96, 1, 1u << 30);
+    if (frames_ok && max_win >= dbl_from) {
+      const size_t tbytes = (size_t)win_total * kWinBytes * 2;
+      if (SB.d_wdbl.reserve(2 * tbytes + 64)) return UNZ_ERR;
+      uint16_t* T[2] = {static_cast<uint16_t*>(SB.d_wdbl.p), reinterpret_cast<uint16_t*>(static_cast<uint8_t*>(SB.d_wdbl.p) + tbytes)};
+      window_double_init_kernel<<<win_total * 16u, 256, 0, st>>>(d_sd, ns, static_cast<uint16_t*>(SB.d_sym.p),
+                                                                 static_cast<uint64_t*>(SB.d_off.p), T[0]);
+      CU_TRY(cudaGetLastError(), "window_double_init_kernel launch");
+      g_launches.fetch_add(1, std::memory_order_relaxed);
+      int cur = 0;
+      for (uint32_t hop = 1;; hop <<= 1) {
+        const bool last = (uint64_t)hop * 2 > max_win;      // after this round hop' = 2 * hop > every window index
+        window_double_round_kernel<<<win_total * 16u, 256, 0, st>>>(d_sd, ns, T[cur], T[cur ^ 1], hop,
+                                                                    last ? static_cast<uint8_t*>(SB.d_wbuf.p) : nullptr);
+        CU_TRY(cudaGetLastError(), "window_double_round_kernel launch");
+        g_launches.fetch_add(1, std::memory_order_relaxed);
+        cur ^= 1;
+        if (last) break;
+      }
+    } else {
+      window_resolve_kernel<<<win_total * 16u, 256, 0, st>>>(d_sd, ns, static_cast<uint16_t*>(SB.d_sym.p),
+                                                             static_cast<uint64_t*>(SB.d_off.p), static_cast<uint8_t*>(SB.d_wbuf.p));
+      CU_TRY(cudaGetLastError(), "window_resolve_kernel launch");
+      g_launches.fetch_add(1, std::memory_order_relaxed);
+    }
   }
   if (blk_total) {
     marker_resolve_kernel<<<(unsigned)blk_total, 256, 0, st>>>(d_sd, ns, static_cast<uint16_t*>(SB.d_sym.p),
@@ -1595,12 +1627,15 @@ UNZ_EXPORT int infl_stream(infl_stream_t* s, const void* src, uint32_t srclen) {
 
   // When to look: a decode attempt is a kernel launch and two small copies, so a caller that feeds single bytes
   // must not pay for one per call.  Look when the caller polls (NULL, 0), while the stream is small, when it has
-  // grown by a sixteenth since the last look, or when this piece is shorter than the one before (the last piece
-  // of a file usually is).  Otherwise the answer is "go on": UNZ_UNFINISHED, as the reference gives for input
+  // grown by a sixteenth since the last look (by 1/128 when the pieces are not tiny), or when this piece is shorter
+  // than the one before (the last piece of a file usually is).  Otherwise the answer is "go on": UNZ_UNFINISHED, as the reference gives for input
   // that ends inside a block (stream.c:614-616).
   const bool shorter = !poll && srclen < s->last_feed;
   if (!poll) s->last_feed = srclen;
-  if (!(poll || s->acc.size() <= 512 || shorter || s->acc.size() - s->tried_at >= (s->tried_at >> 4) + 1)) return UNZ_UNFINISHED;
+  const size_t fresh = s->acc.size() - s->tried_at;
+  if (!(poll || s->acc.size() <= 512 || shorter || fresh >= (s->tried_at >> 4) + 1 ||
+        (srclen >= 64 && fresh >= (s->tried_at >> 7) + 1)))
+    return UNZ_UNFINISHED;
   if (poll && s->tried_at == s->acc.size() && !s->out_moved) {
     // nothing new since the last look: the same verdict without a launch
     return s->last_rc;

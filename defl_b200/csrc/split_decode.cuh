@@ -628,6 +628,54 @@ window_resolve_kernel(const SplitStreamDesc* __restrict__ streams, uint32_t nstr
   *reinterpret_cast<uint2*>(wbuf + (size_t)(c - 1u) * kWinBytes + k0) = make_uint2(lo, hi);
 }
 
+// D1 for streams with long chains of chunks (one deflate history over hundreds of MB): following every marker
+// back chunk by chunk, as window_resolve_kernel does, costs (markers) x (chain length) serial look-ups -- a byte
+// of a common word can travel through thousands of windows.  Pointer doubling instead: T[w][k] is the 32 KiB
+// before chunk w + 1 as 16-bit symbols whose markers index the window `hop` windows earlier (hop = 1 at first:
+// a chunk's markers index the window right before it; needs every inner chunk to produce >= 32 KiB, which the
+// host checks).  One round replaces every marker by the symbol it points at in T[w - hop], which indexes the
+// window 2 * hop back; after ceil(log2(windows)) rounds nothing is left to follow.
+__global__ void __launch_bounds__(256)
+window_double_init_kernel(const SplitStreamDesc* __restrict__ streams, uint32_t nstreams, const uint16_t* __restrict__ sym_all,
+                          const uint64_t* __restrict__ off_all, uint16_t* __restrict__ T) {
+  const uint32_t wi = blockIdx.x / 16u;
+  const SplitStreamDesc& sd = streams[stream_of(nstreams, wi, [&](uint32_t i) { return (uint64_t)streams[i].win_base; })];
+  const uint32_t c  = 1u + (wi - sd.win_base);
+  if (c >= sd.nchunk) return;
+  const uint32_t k0 = (blockIdx.x % 16u) * 2048u + threadIdx.x * 8u;
+  const uint16_t* src = sym_all + sd.sym_base + (off_all + sd.off_base)[c] - kWinBytes + k0;
+  uint16_t*       dst = T + (size_t)wi * kWinBytes + k0;
+#pragma unroll
+  for (int k = 0; k < 8; k++) dst[k] = src[k];           // the tail need not be 16-byte aligned
+}
+
+__global__ void __launch_bounds__(256)
+window_double_round_kernel(const SplitStreamDesc* __restrict__ streams, uint32_t nstreams, const uint16_t* __restrict__ Tin,
+                           uint16_t* __restrict__ Tout, uint32_t hop, uint8_t* __restrict__ wbuf_all) {
+  const uint32_t wi = blockIdx.x / 16u;
+  const SplitStreamDesc& sd = streams[stream_of(nstreams, wi, [&](uint32_t i) { return (uint64_t)streams[i].win_base; })];
+  const uint32_t w  = wi - sd.win_base;
+  if (w + 1u >= sd.nchunk) return;
+  const uint32_t k0 = (blockIdx.x % 16u) * 2048u + threadIdx.x * 8u;
+  const uint4 v = *reinterpret_cast<const uint4*>(Tin + (size_t)wi * kWinBytes + k0);
+  uint32_t s[8] = {v.x & 0xFFFFu, v.x >> 16, v.y & 0xFFFFu, v.y >> 16, v.z & 0xFFFFu, v.z >> 16, v.w & 0xFFFFu, v.w >> 16};
+  if (w >= hop && ((v.x | v.y | v.z | v.w) & 0x80008000u)) {
+    const uint16_t* back = Tin + (size_t)(wi - hop) * kWinBytes;
+#pragma unroll
+    for (int k = 0; k < 8; k++)
+      if (s[k] & 0x8000u) s[k] = back[s[k] & 0x7FFFu];
+  }
+  if (wbuf_all) {                                           // the last round leaves the windows as bytes for D2
+    const uint32_t lo = (s[0] & 255u) | ((s[1] & 255u) << 8) | ((s[2] & 255u) << 16) | (s[3] << 24);
+    const uint32_t hi = (s[4] & 255u) | ((s[5] & 255u) << 8) | ((s[6] & 255u) << 16) | (s[7] << 24);
+    *reinterpret_cast<uint2*>(wbuf_all + (size_t)wi * kWinBytes + k0) = make_uint2(lo, hi);
+  } else {
+    uint4 o;
+    o.x = s[0] | (s[1] << 16); o.y = s[2] | (s[3] << 16); o.z = s[4] | (s[5] << 16); o.w = s[6] | (s[7] << 16);
+    *reinterpret_cast<uint4*>(Tout + (size_t)wi * kWinBytes + k0) = o;
+  }
+}
+
 __global__ void __launch_bounds__(256)
 marker_resolve_kernel(const SplitStreamDesc* __restrict__ streams, uint32_t nstreams, const uint16_t* __restrict__ sym_all,
                       const uint64_t* __restrict__ off_all, const uint8_t* __restrict__ wbuf_all,

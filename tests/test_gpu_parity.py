@@ -189,9 +189,30 @@ def test_infl_stream_shim(gpu_lib, corpus):
             k += 1
             if rc != d.UNZ_UNFINISHED:
                 break
+        polls = 0
+        while rc == d.UNZ_UNFINISHED and polls < 5:          # test_files.c:761-767: a few empty calls
+            rc = st.stream(None)
+            polls += 1
         assert rc == d.UNZ_OK, e["name"]
         assert hashlib.sha256(bytes(st.output())).hexdigest() == e["raw_sha256"], e["name"]
         st.destroy()
+    # byte-wise (test_files.c:792-869): one-byte pieces, then at most 32 empty calls; the library must not pay a
+    # device round trip per byte
+    e = next(x for x in corpus if x["name"] == "png_simulation")
+    st = d.InflStream(e["cap"], 0)
+    l0 = d.kernel_launch_count()
+    rc = d.UNZ_UNFINISHED
+    for i in range(len(e["data"])):
+        rc = st.stream(e["data"][i:i + 1])
+        if rc != d.UNZ_UNFINISHED:
+            break
+    polls = 0
+    while rc == d.UNZ_UNFINISHED and polls < 32:
+        rc = st.stream(None)
+        polls += 1
+    assert rc == d.UNZ_OK and hashlib.sha256(bytes(st.output())).hexdigest() == e["raw_sha256"]
+    assert d.kernel_launch_count() - l0 < 2000, "a launch per byte"
+    st.destroy()
     e = next(x for x in corpus if x["name"] == "png_simulation")
     data = e["data"]
     st = d.InflStream(e["raw_len"] // 2, 0)
