@@ -779,8 +779,9 @@ struct HostPipe {
 HostPipe g_pipes[kMaxDevices];
 
 constexpr size_t kGapMerge   = 512;          // input runs this close in host memory are copied as one
-constexpr size_t kChunkMin   = 96u << 20;    // bytes (in + out) per chunk, at least
-constexpr size_t kChunkCount = 12;           // aim for this many chunks in a large batch
+constexpr size_t kChunkMin   = 64u << 20;    // bytes (in + out) per chunk, at least
+constexpr size_t kChunkCount = 32;           // aim for this many chunks in a large batch (the first chunk's way in and the
+                                             // last one's way out overlap with nothing: keep them small)
 
 int chunk_submit(Engine* E, PipeSlot& S, const infl_batch_item_t* items, size_t first, size_t count, int flags) {
   cudaStream_t st = S.st;
@@ -847,6 +848,13 @@ int chunk_submit(Engine* E, PipeSlot& S, const infl_batch_item_t* items, size_t 
     return UNZ_ERR;
   CU_TRY(cudaMemcpyAsync(S.h_results.p, S.d_results.p, count * sizeof(infl_batch_result_t), cudaMemcpyDeviceToHost, st),
          "D2H results");
+  // the decoded bytes follow in the same stream, whole runs of adjacent destinations at once: no host round trip
+  // between the kernel and the copy.  A stream that failed or produced less than its buffer holds leaves
+  // unspecified bytes after its outlen, as the reference does after its produced length (infl.c:269-376 write
+  // past the end of a match inside dst).
+  for (const HostRun& r : S.out_runs)
+    if (r.len)
+      CU_TRY(cudaMemcpyAsync(const_cast<uint8_t*>(r.h), dout + r.dev_off, r.len, cudaMemcpyDeviceToHost, st), "D2H output");
   return UNZ_OK;
 }
 
@@ -856,21 +864,6 @@ int chunk_finish(PipeSlot& S, const infl_batch_item_t* items, infl_batch_result_
   CU_TRY(cudaStreamSynchronize(st), "inflate kernel");
   auto* hr = static_cast<infl_batch_result_t*>(S.h_results.p);
   uint8_t* dout = static_cast<uint8_t*>(S.d_out.p);
-  // a whole run in one copy when every stream filled its buffer exactly, otherwise only the bytes each produced
-  for (const HostRun& r : S.out_runs) {
-    bool exact = r.len != 0;
-    for (size_t k = r.first; exact && k < r.first + r.count; k++)
-      exact = hr[k].code == UNZ_OK && hr[k].outlen == items[S.first + k].dstlen;
-    if (exact) {
-      CU_TRY(cudaMemcpyAsync(const_cast<uint8_t*>(r.h), dout + r.dev_off, r.len, cudaMemcpyDeviceToHost, st),
-             "D2H output");
-    } else {
-      for (size_t k = r.first; k < r.first + r.count; k++)
-        if (hr[k].outlen)
-          CU_TRY(cudaMemcpyAsync(items[S.first + k].dst, dout + S.out_off[k], hr[k].outlen, cudaMemcpyDeviceToHost, st),
-                 "D2H output");
-    }
-  }
   std::memcpy(results + S.first, hr, S.count * sizeof(*hr));
   return UNZ_OK;
 }
@@ -938,13 +931,12 @@ int run_host_batch_on_device(const infl_batch_item_t* items, size_t n, int flags
       count++;
     }
     PipeSlot& S = HP.slot[c % kPipeSlots];
-    if (c >= kPipeSlots) rc = (cudaStreamSynchronize(S.st) == cudaSuccess) ? UNZ_OK : fail("D2H output");   // its last chunk is home
+    if (c >= kPipeSlots) rc = chunk_finish(S, items, results);      // the chunk that used this slot is home
     if (rc == UNZ_OK) rc = chunk_submit(E, S, items, first, count, flags);
-    if (rc == UNZ_OK && c >= 1) rc = chunk_finish(HP.slot[(c - 1) % kPipeSlots], items, results);
     first += count;
     c++;
   }
-  if (rc == UNZ_OK && c >= 1) rc = chunk_finish(HP.slot[(c - 1) % kPipeSlots], items, results);
+  for (int k = std::max(0, c - kPipeSlots); k < c && rc == UNZ_OK; k++) rc = chunk_finish(HP.slot[k % kPipeSlots], items, results);
   for (PipeSlot& S : HP.slot) {
     const cudaError_t e = cudaStreamSynchronize(S.st);
     if (e != cudaSuccess && rc == UNZ_OK) rc = fail("D2H output", e);
