@@ -98,6 +98,38 @@ oracle_lens_ok(const uint8_t *lens, int n) {
   return 1;
 }
 
+/* infl_ft_build's table budget, infl.c:500-529: a root table of 2^rootbits entries plus, for every root
+   prefix that holds codes longer than the root, a sub-table of 2^(longest such code - rootbits) entries;
+   more than `cap` entries in all => fail (infl.c:524-525; cap 2048 for literal/length at rootbits 10, 512 for
+   distance at rootbits 8, infl.c:382-383).  Reachable: tests/test_table_caps.py has a 32-symbol distance set
+   that needs 534.  The set is known to pass oracle_lens_ok. */
+int
+oracle_table_fits(const uint8_t *lens, int n, unsigned rootbits, unsigned cap) {
+  unsigned count[MAXBITS + 1] = {0}, next[MAXBITS + 1], code = 0, used, l, p;
+  uint8_t        needl[1u << 10];
+  int            i;
+
+  for (i = 0; i < n; i++) count[lens[i]]++;
+  count[0] = 0;
+  for (l = 1; l <= MAXBITS; l++) { code = (code + count[l - 1]) << 1; next[l] = code; }
+  memset(needl, 0, sizeof(needl));
+  for (i = 0; i < n; i++) {
+    l = lens[i];
+    if (!l) continue;
+    code = next[l]++;
+    if (l <= rootbits) continue;
+    p = bitrev(code, l) & ((1u << rootbits) - 1u);
+    if (needl[p] < l - rootbits) needl[p] = (uint8_t)(l - rootbits);
+  }
+  used = 1u << rootbits;
+  for (p = 0; p < (1u << rootbits); p++)
+    if (needl[p]) {
+      if (used + (1u << needl[p]) > cap) return 0;
+      used += 1u << needl[p];
+    }
+  return 1;
+}
+
 static int
 huff_build(hufftab_t *t, const uint8_t *lens, int n) {
   uint16_t offs[MAXBITS + 2];
@@ -253,7 +285,8 @@ dynamic_header(bitreader_t *br, hufftab_t *tlit, hufftab_t *tdist) {
   }
 
   /* :991-997 -- no HLIT<=286 / HDIST<=30 / "has end-of-block" checks, unlike zlib */
-  if (!huff_build(tlit, lens, hlit) || !huff_build(tdist, lens + hlit, hdist))
+  if (!huff_build(tlit, lens, hlit) || !huff_build(tdist, lens + hlit, hdist) ||
+      !oracle_table_fits(lens, (int)hlit, 10, 2048) || !oracle_table_fits(lens + hlit, (int)hdist, 8, 512))
     return ORACLE_ERR;
   return ORACLE_OK;
 }

@@ -40,6 +40,7 @@ int oracle_inflate_chunks(const uint8_t *src, const uint64_t *offs, uint32_t nch
 
 /* accept/reject of a code-length set, as infl_ft_build decides it */
 int oracle_lens_ok(const uint8_t *lens, int n);
+int oracle_table_fits(const uint8_t *lens, int n, unsigned rootbits, unsigned cap);
 
 /* bit offsets (from the start of the deflate body) and output offsets of every block
    header in a valid stream; returns the number of blocks or -1 */

@@ -24,8 +24,7 @@ class StreamOut(ctypes.Structure):
                 ("inpos", ctypes.c_uint32), ("adler_stored", ctypes.c_uint32), ("info", ctypes.c_uint32)]
 
 
-@pytest.fixture(scope="module")
-def emu():
+def load_emu():
     srcs = [os.path.join(EMU_DIR, "emu_main.cpp"), os.path.join(EMU_DIR, "simt_emu.h"), CORE,
             os.path.join(CSRC, "pipeline.cuh"), os.path.join(CSRC, "warp_decode.cuh"),
             os.path.join(CSRC, "warp_decode4.cuh"), os.path.join(CSRC, "split_decode.cuh")]
@@ -33,6 +32,11 @@ def emu():
         subprocess.check_call(["g++", "-std=c++17", "-O1", "-fPIC", "-shared", "-pthread", "-w",
                                "-o", EMU_SO, srcs[0]])
     return ctypes.CDLL(EMU_SO)
+
+
+@pytest.fixture(scope="module")
+def emu():
+    return load_emu()
 
 
 def run(emu, G, data, cap, flags, mis=0):
