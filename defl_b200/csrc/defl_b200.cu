@@ -100,7 +100,7 @@ struct Engine {
   DevBuf       d_in, d_out, d_items, d_results, d_order, d_ws, d_seg, d_stage;
   DevBuf       d_items2, d_results2, d_order2, d_ws2;
   PinBuf       h_items, h_results, h_order, h_pack, h_seg;
-  bool         ready = false;
+  std::atomic<bool> ready{false};   // set with release once stream / sms are in place (double-checked under g_engine_mu)
 };
 
 constexpr int kMaxDevices = 16;
@@ -112,9 +112,9 @@ int engine_for_current_device(Engine** out) {
   CU_TRY(cudaGetDevice(&dev), "cudaGetDevice (is a CUDA device visible? this library has no CPU path)");
   if (dev < 0 || dev >= kMaxDevices) return fail("device index out of range");
   Engine& e = g_engines[dev];
-  if (!e.ready) {
+  if (!e.ready.load(std::memory_order_acquire)) {
     std::lock_guard<std::mutex> g(g_engine_mu);
-    if (!e.ready) {
+    if (!e.ready.load(std::memory_order_relaxed)) {
       cudaDeviceProp prop;
       CU_TRY(cudaGetDeviceProperties(&prop, dev), "cudaGetDeviceProperties");
       if (prop.major < 10) return fail("this build contains sm_100a code only (needs a B200-class GPU)");
@@ -122,7 +122,7 @@ int engine_for_current_device(Engine** out) {
       e.sms = prop.multiProcessorCount;
       CU_TRY(cudaStreamCreateWithFlags(&e.stream, cudaStreamNonBlocking), "cudaStreamCreate");
       CU_TRY(cudaStreamCreateWithFlags(&e.stream2, cudaStreamNonBlocking), "cudaStreamCreate");
-      e.ready = true;
+      e.ready.store(true, std::memory_order_release);
     }
   }
   *out = &e;
@@ -135,7 +135,7 @@ int launch_batch(int sms, const infl_batch_item_t* d_items, const uint32_t* d_or
                  infl_batch_result_t* d_results, unsigned int* d_ticket, cudaStream_t st) {
   auto         kern = defl::inflate_batch_kernel<G, GROUPS>;
   const size_t smem = sizeof(GroupSmem) * GROUPS;
-  static int   ctas_per_sm[kMaxDevices] = {0};
+  static std::atomic<int> ctas_per_sm[kMaxDevices];   // zero-initialised; racing first callers compute the same value
   int          dev = 0;
   cudaGetDevice(&dev);
   if (!ctas_per_sm[dev]) {
@@ -164,7 +164,7 @@ int launch_pipeline(int sms, const infl_batch_item_t* d_items, const uint32_t* d
                     infl_batch_result_t* d_results, unsigned int* d_ticket, cudaStream_t st) {
   auto             kern = defl::inflate_pipeline_kernel<D, SL, K>;
   constexpr size_t smem = defl::pipeline_smem_bytes<D, SL, K>();
-  static int       ctas_per_sm[kMaxDevices] = {0};
+  static std::atomic<int> ctas_per_sm[kMaxDevices];
   int              dev = 0;
   cudaGetDevice(&dev);
   if (!ctas_per_sm[dev]) {
@@ -192,7 +192,7 @@ constexpr size_t kWsHeader    = 256;     // ticket counter and friends live in f
 int warp_kernel_grid(int sms, int* grid_out) {
   auto         kern = defl::inflate_warp_kernel<kWarpsPerCta>;
   const size_t smem = sizeof(defl::WarpSmem) * kWarpsPerCta;
-  static int   ctas_per_sm[kMaxDevices] = {0};
+  static std::atomic<int> ctas_per_sm[kMaxDevices];   // zero-initialised; racing first callers compute the same value
   int          dev = 0;
   cudaGetDevice(&dev);
   if (!ctas_per_sm[dev]) {
@@ -210,7 +210,7 @@ int warp_kernel_grid(int sms, int* grid_out) {
 // ---- v4 (default engine): warp per stream, 64-bit tokens, shared-memory rings and stage ----------------------
 int warp4_kernel_grid(int sms, int* grid_out) {        // in warps = CTAs
   auto       kern = defl::inflate_warp4_kernel;
-  static int ctas_per_sm[kMaxDevices] = {0};
+  static std::atomic<int> ctas_per_sm[kMaxDevices];
   int        dev = 0;
   cudaGetDevice(&dev);
   if (!ctas_per_sm[dev]) {
@@ -563,6 +563,7 @@ int split_decode_many(Engine* E, const SplitInput* in, size_t nin, int flags, vo
       const bool ends_here = fin == FIN_YES && k != 0 && o[k].has_eob;       // its first block was the last one
       if (fin == FIN_YES && k != 0 && !o[k].has_eob && o[k].status != CH_LINKED) { ok = false; break; }
       const uint32_t bytes = ends_here ? o[k].eob_bytes : o[k].out_bytes;
+      if (bytes >= 0x80000000u) { ok = false; break; }   // resolve_tokens<uint16_t> compares chunk-relative positions as int32
       chain.push_back({i, k, total, bytes, ends_here ? o[k].eob_ntok : o[k].ntok, k == 0 ? (uint32_t)FIN_NO : fin, ends_here});
       off.push_back(total);
       total += bytes;
@@ -794,9 +795,13 @@ int chunk_submit(Engine* E, PipeSlot& S, const infl_batch_item_t* items, size_t 
   for (size_t k = 0; k < count; k++) {
     const infl_batch_item_t& it = items[first + k];
     const uint8_t* s = static_cast<const uint8_t*>(it.src);
-    if (!in_runs.empty() && s >= in_runs.back().h + in_runs.back().len &&
+    if (it.srclen == 0) {
+      // nothing to copy, and its pointer may be anything: it neither starts nor extends a run
+      in_off[k] = 0;
+    } else if (!in_runs.empty() && s >= in_runs.back().h + in_runs.back().len &&
         (size_t)(s - (in_runs.back().h + in_runs.back().len)) <= kGapMerge) {
-      // the gap lies between two buffers the caller owns, inside pages they touch: copy it along
+      // the gap (<= 512 bytes) lies between two non-empty buffers of the caller, so inside the page of the last byte
+      // of the one or of the first byte of the other: mapped memory.  Copy it along.
       HostRun& r = in_runs.back();
       in_off[k] = r.dev_off + (size_t)(s - r.h);
       r.len = (size_t)(s - r.h) + it.srclen;
@@ -807,7 +812,7 @@ int chunk_submit(Engine* E, PipeSlot& S, const infl_batch_item_t* items, size_t 
       in_runs.push_back({s, (size_t)it.srclen, in_total, k, 1});
       in_off[k] = in_total;
     }
-    in_total = in_runs.back().dev_off + in_runs.back().len;
+    if (!in_runs.empty()) in_total = in_runs.back().dev_off + in_runs.back().len;
 
     const uint8_t* d = static_cast<const uint8_t*>(it.dst);
     if (!S.out_runs.empty() && d == S.out_runs.back().h + S.out_runs.back().len) {
