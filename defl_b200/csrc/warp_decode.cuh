@@ -53,6 +53,8 @@ enum : uint32_t { LS_OK = 0, LS_EOB = 1, LS_FULL = 2, LS_FAIL = 3, LS_NONE = 4 }
 struct WarpSmem {
   uint16_t lit[kLitTab];
   uint16_t dist[kDistTab];
+  uint32_t stop_lane;            // speculative pass: the lowest lane that met the end of the block (or no code)
+  uint32_t pad_[3];
   union {
     BuildScratch s;              // while a block header is parsed
     uint16_t     stage[kStageV3];  // while tokens are resolved (bytes, or 16-bit symbols in split decode)
@@ -199,7 +201,8 @@ struct LaneTraj {
 // running pointers for the token and checkpoint stores.
 DEFL_DEV void lane_spec(const uint16_t* lit, const uint16_t* dist, const uint32_t* words, uint32_t wend,
                         uint32_t bw, uint32_t start, uint32_t limit, uint32_t endr, uint32_t* seg,
-                        uint16_t* cps, LaneTraj& tj, uint32_t warm, uint32_t* ring_lane) {
+                        uint16_t* cps, LaneTraj& tj, uint32_t warm, uint32_t* ring_lane,
+                        uint32_t* stop_lane = nullptr, uint32_t lane = 0) {
   SubReader br;
   br.w = words; br.wend = wend;
   uint32_t r = start;
@@ -260,11 +263,15 @@ DEFL_DEV void lane_spec(const uint16_t* lit, const uint16_t* dist, const uint32_
       if (r >= next_cp) {
         *cpp++ = (uint16_t)((r - next_cp) | ((uint32_t)(tp - seg) << 6));
         next_cp += kCpBits;
+        // a lane below met the end of the block: most likely nothing from here on belongs to it.  Stop as if the
+        // token segment was full (if that lane was off the true trajectory, the next window starts here).
+        if (stop_lane && lane > *reinterpret_cast<volatile uint32_t*>(stop_lane)) { stat = LS_FULL; break; }
       }
       *tp++ = tok;
       r += used;
       rr.consume(used);
     }
+    if (stat == LS_FULL) break;
     // ---- one careful step: the ends of the sub-sequence, the input and the block, failures
     if (r >= limit) break;
     if (tp == tend) { stat = LS_FULL; break; }
@@ -284,6 +291,7 @@ DEFL_DEV void lane_spec(const uint16_t* lit, const uint16_t* dist, const uint32_
     rr.consume(used);
   }
   rr.drain();
+  if (stop_lane && (stat == LS_EOB || (stat & 0xFFu) == LS_FAIL)) simt::atomic_min_shared(stop_lane, lane);
   const uint32_t t = (uint32_t)(tp - seg);
   tj.land = r; tj.stat = stat; tj.n = t; tj.m = 0; tj.nf = 0; tj.T = r0; tj.ncp = (uint32_t)(cpp - cps);
   tj.s_land = r; tj.s_stat = stat; tj.s_n = t;
@@ -363,9 +371,17 @@ template <> struct SymWord<uint16_t> { static constexpr uint32_t kPer = 2, kShif
 // a lane copies matches of up to this many words' worth of symbols itself (bytes / 16-bit symbols)
 template <typename SYM> struct LaneWords { static constexpr uint32_t k = sizeof(SYM) == 2 ? DEFL_LANE_WORDS16 : DEFL_LANE_WORDS; };
 
+// Adler-32 partial sums of the bytes a lane has sent to dst (order-free form: sum x and sum (position - base) * x),
+// taken from the very words the resolver stores -- no second pass over the output.
+struct AdlerAcc {
+  uint32_t ta;
+  uint64_t tw;
+  uint32_t base;
+};
+
 template <typename SYM>
 DEFL_DEV uint32_t resolve_tokens(uint16_t* stage_mem, int lane, const uint32_t* toks, uint32_t count, SYM* dst0,
-                                 uint32_t cap, uint32_t& P, uint32_t hist) {
+                                 uint32_t cap, uint32_t& P, uint32_t hist, AdlerAcc* ad = nullptr) {
   using SW = SymWord<SYM>;
   constexpr uint32_t kPer = SW::kPer;
   constexpr uint32_t kLaneWords = LaneWords<SYM>::k;
@@ -525,14 +541,39 @@ DEFL_DEV uint32_t resolve_tokens(uint16_t* stage_mem, int lane, const uint32_t* 
       const uint32_t w_lo  = (a0 + kPer - 1u) >> SW::kShift;
       const uint32_t w_hi  = s_end >> SW::kShift;
       uint32_t* const gw = reinterpret_cast<uint32_t*>((uintptr_t)dst & ~(uintptr_t)3);     // word of stage word 0
+      uint32_t bs = 0, bq = 0;               // this lane's bytes of the batch: sum x, sum (offset in the batch) * x
       if (w_hi > w_lo) {
-        for (uint32_t w = w_lo + (uint32_t)lane; w < w_hi; w += 32u) gw[w] = stw[w];
+        for (uint32_t w = w_lo + (uint32_t)lane; w < w_hi; w += 32u) {
+          const uint32_t v = stw[w];
+          gw[w] = v;
+          if (sizeof(SYM) == 1 && ad) {
+            const uint32_t sv = simt::dp4a(v, 0x01010101u, 0u);
+            bs += sv;
+            bq += ((w << 2) - a0) * sv + simt::dp4a(v, 0x03020100u, 0u);
+          }
+        }
         const uint32_t head = (w_lo << SW::kShift) - a0;                    // < kPer
         const uint32_t tail = s_end - (w_hi << SW::kShift);                 // < kPer
-        if ((uint32_t)lane < head) dst[lane] = st[a0 + lane];
-        if ((uint32_t)lane < tail) dst[B - tail + lane] = st[s_end - tail + lane];
+        if ((uint32_t)lane < head) {
+          const SYM b = st[a0 + lane];
+          dst[lane] = b;
+          if (sizeof(SYM) == 1 && ad) { bs += b; bq += (uint32_t)lane * b; }
+        }
+        if ((uint32_t)lane < tail) {
+          const SYM b = st[s_end - tail + lane];
+          dst[B - tail + lane] = b;
+          if (sizeof(SYM) == 1 && ad) { bs += b; bq += (B - tail + lane) * b; }
+        }
       } else {
-        if ((uint32_t)lane < B) dst[lane] = st[a0 + lane];                  // B < 2 * kPer here
+        if ((uint32_t)lane < B) {                                           // B < 2 * kPer here
+          const SYM b = st[a0 + lane];
+          dst[lane] = b;
+          if (sizeof(SYM) == 1 && ad) { bs += b; bq += (uint32_t)lane * b; }
+        }
+      }
+      if (sizeof(SYM) == 1 && ad) {
+        ad->ta += bs;
+        ad->tw += (uint64_t)(P - ad->base) * bs + bq;
       }
     }
     P += B;
@@ -573,7 +614,7 @@ template <typename SYM, bool COUNT>
 DEFL_DEV uint32_t decode_window(WarpSmem& sm, const WarpScratch& sc, int lane, const uint32_t* words,
                                 uint32_t wend, uint64_t end_bit, uint64_t& cur, SYM* dst, uint32_t cap,
                                 uint32_t& pos, uint32_t hist, TokSink* sink = nullptr,
-                                uint64_t soft_end = ~0ull, uint32_t warm_bits = kWarmDynamic) {
+                                uint64_t soft_end = ~0ull, uint32_t warm_bits = kWarmDynamic, AdlerAcc* ad = nullptr) {
   // soft_end (> cur): no token that STARTS at or after this bit is decoded in this window, so the window ends on
   // the first token boundary >= soft_end (the caller compares `cur` with it: split decode links chunks there)
   const uint32_t bw   = (uint32_t)(cur >> 5);
@@ -599,8 +640,11 @@ DEFL_DEV uint32_t decode_window(WarpSmem& sm, const WarpScratch& sc, int lane, c
   tj.s_land = start; tj.s_stat = LS_NONE; tj.s_n = 0;
   const uint32_t warm = (lane >= 1 && active) ? (warm_bits < S ? warm_bits : S) : 0u;      // lane 0 starts on a known boundary
   // the resolver's stage is idle during the speculative pass: it holds the lanes' input rings
+  if (lane == 0) sm.stop_lane = 32u;
+  simt::syncwarp(kFull);
   if (active) lane_spec(sm.lit, sm.dist, words, wend, bw, start, limit, endr, seg, cps, tj, warm,
-                        reinterpret_cast<uint32_t*>(sm.stage) + lane * 4);
+                        reinterpret_cast<uint32_t*>(sm.stage) + lane * 4,
+                        nullptr, (uint32_t)lane);   // early stop past a lower lane's end of block: tried, slower
   simt::syncwarp(kFull);
 
   // fix-up rounds until every lane starts where its predecessor ended
@@ -674,9 +718,9 @@ DEFL_DEV uint32_t decode_window(WarpSmem& sm, const WarpScratch& sc, int lane, c
       const uint32_t nf = simt::shfl(kFull, tj.nf, L);
       const uint32_t m  = simt::shfl(kFull, tj.m, L);
       const uint32_t n  = simt::shfl(kFull, tj.n, L);
-      if (nf) reason = resolve_tokens<SYM>(sm.stage, lane, sc.fix + (uint32_t)L * kFixCap, nf, dst, cap, pos, hist);
+      if (nf) reason = resolve_tokens<SYM>(sm.stage, lane, sc.fix + (uint32_t)L * kFixCap, nf, dst, cap, pos, hist, ad);
       if (reason == R_NONE && n > m)
-        reason = resolve_tokens<SYM>(sm.stage, lane, sc.spec + (uint32_t)L * kSpecCap + m, n - m, dst, cap, pos, hist);
+        reason = resolve_tokens<SYM>(sm.stage, lane, sc.spec + (uint32_t)L * kSpecCap + m, n - m, dst, cap, pos, hist, ad);
     }
   }
   if (reason) return fail_stat(reason);
@@ -725,6 +769,12 @@ DEFL_DEV void inflate_stream_warp(WarpSmem& sm, const WarpScratch& sc, int lane,
 
   uint32_t reason = R_NONE;
   bool     fixed_ready = false;
+  // Adler-32: from the resolver's own stores (and over a stored block right after its copy); a stream that is
+  // taken up at a block boundary (infl_stream) sums its whole output once it is complete instead
+  const bool fused = rs == nullptr;
+  uint32_t A = 0, W = 0;
+  AdlerAcc ad;
+  ad.ta = 0; ad.tw = 0; ad.base = 0;
 #pragma unroll 1
   for (;;) {
     if ((int64_t)(end_bit - br.bitpos()) < 3) { reason = R_TRUNCATED; break; }
@@ -732,8 +782,10 @@ DEFL_DEV void inflate_stream_warp(WarpSmem& sm, const WarpScratch& sc, int lane,
     const uint32_t bfinal = hdr & 1u, btype = (hdr >> 1) & 3u;
     br.skip(3); br.norm();
     if (btype == 0) {
+      const uint32_t pos0 = pos;
       reason = stored_block<32>(L, br, src, srclen, base_bit, dst, pos, cap);
       if (reason) break;
+      if (fused) { simt::syncwarp(kFull); adler_range<32>(L, dst, pos0, pos, A, W); }
     } else if (btype == 3) {
       reason = R_BLOCK_TYPE;
       break;
@@ -746,8 +798,15 @@ DEFL_DEV void inflate_stream_warp(WarpSmem& sm, const WarpScratch& sc, int lane,
       uint32_t st;
 #pragma unroll 1
       do {
+        ad.base = pos;
         st = decode_window<uint8_t, false>(sm, sc, lane, br.w, br.wend, end_bit, cur, dst, cap, pos, 0u, nullptr, ~0ull,
-                                           btype == 1u ? kWarmFixed : kWarmDynamic);
+                                           btype == 1u ? kWarmFixed : kWarmDynamic, fused ? &ad : nullptr);
+        if (fused) {                                   // fold this window's sums (positions relative to its start)
+          const uint32_t a = ad.ta % kAdlerMod;
+          A = (A + a) % kAdlerMod;
+          W = (uint32_t)((W + (uint64_t)(ad.base % kAdlerMod) * a + ad.tw % kAdlerMod) % kAdlerMod);
+          ad.ta = 0; ad.tw = 0;
+        }
       } while (st == LS_OK);
       if (st != LS_EOB) { reason = st >> 8; break; }
       br.seek(cur);
@@ -759,9 +818,8 @@ DEFL_DEV void inflate_stream_warp(WarpSmem& sm, const WarpScratch& sc, int lane,
   }
   if (reason) { out.info = reason << 8; out.outlen = pos; return; }
 
-  uint32_t A = 0, W = 0;
   simt::syncwarp(kFull);
-  adler_range<32>(L, dst, 0, pos, A, W);
+  if (!fused) adler_range<32>(L, dst, 0, pos, A, W);
   finish_stream<32>(L, src, srclen, pos, br.bitpos() - base_bit, A, W, zlib, flags, out);
 }
 

@@ -202,6 +202,8 @@ constexpr uint32_t kCpMax    = 96;        // checkpoints per lane: (warm-up toke
 DEFL_DEV void lane_spec4(const uint16_t* lit, const uint16_t* dist, const Input4& in, uint32_t base_quad,
                          uint32_t bw, uint32_t start, uint32_t limit, uint32_t endr, uint2* seg, uint32_t* cps,
                          LaneTraj& tj, uint32_t warm, uint32_t* ring_lane, uint32_t* stop_lane, uint32_t lane) {
+  // stop_lane: nullptr inside fixed-Huffman blocks (a lane that starts blind there meets the 7-bit end-of-block code
+  // within a few symbols: the hint would be wrong most of the time)
   uint32_t r = start - warm, r0 = start;
   Ring4 rg;
   rg.init(ring_lane, in, base_quad, r);
@@ -217,7 +219,7 @@ DEFL_DEV void lane_spec4(const uint16_t* lit, const uint16_t* dist, const Input4
       // a lane below met the end of the block (or something that is no code): most likely everything from
       // here on is not part of the block.  Stop as if the token segment was full; if that lane turns out to
       // have been off the true trajectory, the next window simply starts here.
-      if (lane > *reinterpret_cast<volatile uint32_t*>(stop_lane) || ti + 4u > kSpecCap) {
+      if ((stop_lane && lane > *reinterpret_cast<volatile uint32_t*>(stop_lane)) || ti + 4u > kSpecCap) {
         if (!keep) { r0 = start; r = start; }
         stat = LS_FULL;
         break;
@@ -318,7 +320,7 @@ DEFL_DEV void lane_spec4(const uint16_t* lit, const uint16_t* dist, const Input4
     }
   }
   rg.drain();
-  if (stat == LS_EOB || (stat & 0xFFu) == LS_FAIL) simt::atomic_min_shared(stop_lane, lane);
+  if (stop_lane && (stat == LS_EOB || (stat & 0xFFu) == LS_FAIL)) simt::atomic_min_shared(stop_lane, lane);
   tj.land = r; tj.stat = stat; tj.n = ti; tj.m = 0; tj.nf = 0; tj.T = r0; tj.ncp = ncp;
   tj.s_land = r; tj.s_stat = stat; tj.s_n = ti;
 }
@@ -674,7 +676,7 @@ DEFL_DEV uint32_t decode_window4(WarpSmem4& sm, const WarpScratch4& sc, int lane
   if (lane == 0) sm.stop_lane = 32u;
   simt::syncwarp(kFull);                                                // the stage is the lanes' input rings now
   if (active) lane_spec4(sm.lit, sm.dist, in, base_quad, bw, start, limit, endr, seg, cps, tj, warm,
-                         sm.ring + lane * kRingWords, &sm.stop_lane, (uint32_t)lane);
+                         sm.ring + lane * kRingWords, warm_bits == kWarmDynamic ? &sm.stop_lane : nullptr, (uint32_t)lane);
   simt::syncwarp(kFull);
 
   // fix-up rounds until every lane starts where its predecessor ended
