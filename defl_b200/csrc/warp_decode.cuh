@@ -42,7 +42,10 @@ static_assert(kWarpScratchBytes % 16 == 0, "scratch slices stay 16-byte aligned"
 #endif
 constexpr uint32_t kWarmDynamic = DEFL_WARM_DYNAMIC;  // bits a lane decodes ahead of its sub-sequence to get in step (dynamic codes)
 constexpr uint32_t kWarmFixed   = DEFL_WARM_FIXED;    // fixed-Huffman codes are nearly fixed-length and re-synchronise slowly
-constexpr int      kStageV3   = 512;                  // output bytes resolved per token batch
+#ifndef DEFL_STAGE_V3
+#define DEFL_STAGE_V3 512
+#endif
+constexpr int      kStageV3   = DEFL_STAGE_V3;                  // output bytes resolved per token batch
 constexpr uint32_t kTokIsMatch = 0x80000000u;         // [8:0] length, [23:9] distance - 1
 constexpr uint32_t kTokIsDep   = 0x40000000u;         // resolver-side mark
                                                       // literal token: [26:24] count (1..2), [23:0] bytes
