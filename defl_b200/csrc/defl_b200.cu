@@ -96,6 +96,7 @@ struct Engine {
   int          sms      = 0;
   cudaStream_t stream   = nullptr;
   cudaStream_t stream2  = nullptr;   // the one-warp kernel of a batch that also has split-decoded members
+  cudaStream_t stream3  = nullptr;   // chunk-list batches: the decoded bytes of one group go home while the next group decodes
   std::mutex   mu;
   DevBuf       d_in, d_out, d_items, d_results, d_order, d_ws, d_seg, d_stage;
   DevBuf       d_items2, d_results2, d_order2, d_ws2;
@@ -122,6 +123,7 @@ int engine_for_current_device(Engine** out) {
       e.sms = prop.multiProcessorCount;
       CU_TRY(cudaStreamCreateWithFlags(&e.stream, cudaStreamNonBlocking), "cudaStreamCreate");
       CU_TRY(cudaStreamCreateWithFlags(&e.stream2, cudaStreamNonBlocking), "cudaStreamCreate");
+      CU_TRY(cudaStreamCreateWithFlags(&e.stream3, cudaStreamNonBlocking), "cudaStreamCreate");
       e.ready.store(true, std::memory_order_release);
     }
   }
@@ -304,6 +306,8 @@ void size_order(const infl_batch_item_t* items, size_t n, uint32_t* order) {
   std::stable_sort(order, order + n, [&](uint32_t a, uint32_t b) { return work(a) > work(b); });
 }
 
+constexpr size_t kCopyThreshold = 8192;   // pieces up to this size are copied by the reference (src/common.h:46)
+constexpr size_t kGatherPiece   = 65536;  // bytes one gather descriptor covers, at most
 constexpr size_t kAlign = 16;
 inline size_t align_up(size_t v) { return (v + kAlign - 1) & ~(kAlign - 1); }
 
@@ -1185,7 +1189,7 @@ UNZ_EXPORT int infl_gather_device(const void* const* d_seg_src, const uint64_t* 
   if (nseg == 0) return UNZ_OK;
   Engine* E = nullptr;
   if (engine_for_current_device(&E) != UNZ_OK) return UNZ_ERR;
-  const uint64_t warps  = std::min<uint64_t>(nseg, (uint64_t)E->sms * 64);
+  const uint64_t warps  = std::min<uint64_t>((nseg + 31) / 32, (uint64_t)E->sms * 64);   // a warp takes 32 pieces at a time
   const unsigned blocks = (unsigned)((warps * 32 + 255) / 256);
   defl::gather_pieces_kernel<<<blocks, 256, 0, static_cast<cudaStream_t>(cuda_stream)>>>(
       d_seg_src, d_seg_len, d_seg_dst_off, nseg, static_cast<uint8_t*>(d_out));
@@ -1217,15 +1221,14 @@ UNZ_EXPORT int infl_buf_batch(const infl_batch_item_t* items, size_t n, int flag
 
 // Chunk-list batch.  Pieces are never joined by the host CPU:
 //  * device pieces: a (src, len, dst offset) descriptor table drives gather_pieces_kernel;
-//  * host pieces >= 8 KiB: one DMA each, landing at their logical offset in HBM;
-//  * host pieces < 8 KiB are packed into a pinned bounce buffer on their way to the copy
-//    engine (the reference packs exactly these itself, mem.c:121-155, threshold common.h:46).
-UNZ_EXPORT int infl_buf_batch_iov(const infl_batch_iov_item_t* items, size_t n, int flags,
-                                  infl_batch_result_t* results) {
-  if (n == 0) return UNZ_OK;
-  if (!items || !results) return fail("null argument");
-  Engine* E = nullptr;
-  if (engine_for_current_device(&E) != UNZ_OK) return UNZ_ERR;
+//  * host pieces that lie next to each other in memory (gaps <= 512 bytes: IDAT chunks of one file) travel as one
+//    DMA into a staging area, pieces >= 8 KiB elsewhere as one DMA each, and scattered pieces < 8 KiB are packed
+//    into a pinned bounce buffer that travels as one DMA (the reference copies exactly these itself,
+//    mem.c:121-155, threshold common.h:46); gather_pieces_kernel then puts every piece at its logical offset.
+// One group of a chunk-list batch.  out_base: where this group's outputs start in E->d_out (the buffer holds the
+// whole batch, so the copy back of a group can run on E->stream3 while the next group decodes).
+static int iov_group(Engine* E, const infl_batch_iov_item_t* items, size_t n, int flags, infl_batch_result_t* results,
+                     size_t out_base) {
 
   const bool dev_ptrs = (flags & INFL_BATCH_DEVICE_PTRS) != 0;
   std::vector<size_t> in_off(n + 1, 0), out_off(n + 1, 0);
@@ -1242,17 +1245,20 @@ UNZ_EXPORT int infl_buf_batch_iov(const infl_batch_iov_item_t* items, size_t n, 
 
   std::vector<infl_batch_item_t>   flat(n);
   std::vector<infl_batch_result_t> res(n);
-  std::vector<uint32_t>            live;   // streams that actually have pieces
   int rc = UNZ_OK;
   {
-    std::lock_guard<std::mutex> guard(E->mu);
     cudaStream_t st = E->stream;
-    if (E->d_in.reserve(in_off[n] + 64) || (!dev_ptrs && E->d_out.reserve(out_off[n] + 64))) return UNZ_ERR;
+    if (E->d_in.reserve(in_off[n] + 64)) return UNZ_ERR;
     uint8_t* din  = static_cast<uint8_t*>(E->d_in.p);
-    uint8_t* dout = static_cast<uint8_t*>(E->d_out.p);
+    uint8_t* dout = static_cast<uint8_t*>(E->d_out.p) + out_base;
 
     if (dev_ptrs) {
       // descriptor table -> K2
+      // a descriptor covers at most 64 KiB: a warp of the gather kernel takes 32 descriptors at a time, so a
+      // few huge pieces still spread over the whole GPU
+      nseg = 0;
+      for (size_t i = 0; i < n; i++)
+        for (uint64_t k = 0; k < items[i].niov; k++) nseg += (items[i].iov[k].len + kGatherPiece - 1) / kGatherPiece;
       if (E->h_seg.reserve(nseg * 24 + 64) || E->d_seg.reserve(nseg * 24 + 64)) return UNZ_ERR;
       auto* hs_src = static_cast<const void**>(E->h_seg.p);
       auto* hs_len = reinterpret_cast<uint64_t*>(hs_src + nseg);
@@ -1260,8 +1266,11 @@ UNZ_EXPORT int infl_buf_batch_iov(const infl_batch_iov_item_t* items, size_t n, 
       size_t s = 0;
       for (size_t i = 0; i < n; i++) {
         size_t at = in_off[i];
-        for (uint64_t k = 0; k < items[i].niov; k++, s++) {
-          hs_src[s] = items[i].iov[k].ptr; hs_len[s] = items[i].iov[k].len; hs_off[s] = at;
+        for (uint64_t k = 0; k < items[i].niov; k++) {
+          const uint8_t* p = static_cast<const uint8_t*>(items[i].iov[k].ptr);
+          for (uint64_t o = 0; o < items[i].iov[k].len; o += kGatherPiece, s++) {
+            hs_src[s] = p + o; hs_len[s] = std::min<uint64_t>(kGatherPiece, items[i].iov[k].len - o); hs_off[s] = at + o;
+          }
           at += items[i].iov[k].len;
         }
       }
@@ -1275,11 +1284,21 @@ UNZ_EXPORT int infl_buf_batch_iov(const infl_batch_iov_item_t* items, size_t n, 
       // Host pieces.  Pieces that lie (nearly) next to each other in host memory -- the IDAT chunks of a PNG file are
       // 12 bytes apart -- travel as ONE copy, gaps included, into a staging area that keeps the host layout; the
       // gather kernel then joins them on the device.  Pieces that are exactly adjacent share one descriptor.
+      // Pieces scattered over the heap each take a copy of their own (one cudaMemcpyAsync per span).
+      // A small piece (< 8 KiB, the reference's own copy threshold, common.h:46 / mem.c:121-155) that does not
+      // continue the previous span is packed into a pinned bounce buffer, and all of those travel as one copy.
       struct Span { const uint8_t* h; size_t len; size_t dev_off; };
-      struct Seg  { uint32_t span; size_t span_off; size_t len; size_t dst_off; };
+      struct Seg  { uint32_t span; size_t span_off; size_t len; size_t dst_off; };   // span == kBounce: offset into the bounce area
+      constexpr uint32_t kBounce = 0xFFFFFFFFu;
       std::vector<Span> spans;
       std::vector<Seg>  segs;
-      size_t stage_total = 0;
+      size_t stage_total = 0, small_total = 0;
+      for (size_t i = 0; i < n; i++)
+        for (uint64_t k = 0; k < items[i].niov; k++)
+          if (items[i].iov[k].len < kCopyThreshold) small_total += items[i].iov[k].len;
+      if (E->h_pack.reserve(small_total + 64)) return UNZ_ERR;
+      uint8_t* const pack = static_cast<uint8_t*>(E->h_pack.p);
+      size_t bounce_used = 0;
       for (size_t i = 0; i < n; i++) {
         size_t at = in_off[i];
         bool   first = true;
@@ -1288,7 +1307,7 @@ UNZ_EXPORT int infl_buf_batch_iov(const infl_batch_iov_item_t* items, size_t n, 
           const size_t  len = items[i].iov[k].len;
           if (!len) continue;
           bool extend = false;
-          if (!spans.empty()) {
+          if (!spans.empty()) {                         // continues the last span (whatever went to the bounce area since)
             const uint8_t* end = spans.back().h + spans.back().len;
             extend = p >= end && (size_t)(p - end) <= kGapMerge;
           }
@@ -1300,27 +1319,47 @@ UNZ_EXPORT int infl_buf_batch_iov(const infl_batch_iov_item_t* items, size_t n, 
             sp.len = off + len;
             if (glued) segs.back().len += len;
             else segs.push_back({(uint32_t)(spans.size() - 1), off, len, at});
+            stage_total = sp.dev_off + sp.len;
+          } else if (len < kCopyThreshold) {
+            std::memcpy(pack + bounce_used, p, len);
+            const bool glued = !first && !segs.empty() && segs.back().span == kBounce &&
+                               segs.back().span_off + segs.back().len == bounce_used;
+            if (glued) segs.back().len += len;
+            else segs.push_back({kBounce, bounce_used, len, at});
+            bounce_used += len;
           } else {
             stage_total = align_up(stage_total);
             spans.push_back({p, len, stage_total});
             segs.push_back({(uint32_t)(spans.size() - 1), 0, len, at});
+            stage_total = spans.back().dev_off + spans.back().len;
           }
-          stage_total = spans.back().dev_off + spans.back().len;
           at += len;
           first = false;
         }
       }
+      const size_t bounce_base = align_up(stage_total);
+      {   // descriptors of at most 64 KiB (see above)
+        std::vector<Seg> cut;
+        cut.reserve(segs.size());
+        for (const Seg& g : segs)
+          for (size_t o = 0; o < g.len; o += kGatherPiece)
+            cut.push_back({g.span, g.span_off + o, std::min<size_t>(kGatherPiece, g.len - o), g.dst_off + o});
+        segs.swap(cut);
+      }
       const size_t ns2 = segs.size();
       if (ns2) {
-        if (E->d_stage.reserve(stage_total + 64) || E->h_seg.reserve(ns2 * 24 + 64) || E->d_seg.reserve(ns2 * 24 + 64)) return UNZ_ERR;
+        if (E->d_stage.reserve(bounce_base + bounce_used + 64) || E->h_seg.reserve(ns2 * 24 + 64) || E->d_seg.reserve(ns2 * 24 + 64)) return UNZ_ERR;
         uint8_t* dstage = static_cast<uint8_t*>(E->d_stage.p);
         for (const Span& sp : spans)
           CU_TRY(cudaMemcpyAsync(dstage + sp.dev_off, sp.h, sp.len, cudaMemcpyHostToDevice, st), "H2D pieces");
+        if (bounce_used)
+          CU_TRY(cudaMemcpyAsync(dstage + bounce_base, pack, bounce_used, cudaMemcpyHostToDevice, st), "H2D small pieces");
         auto* hs_src = static_cast<const void**>(E->h_seg.p);
         auto* hs_len = reinterpret_cast<uint64_t*>(hs_src + ns2);
         auto* hs_off = hs_len + ns2;
         for (size_t k = 0; k < ns2; k++) {
-          hs_src[k] = dstage + spans[segs[k].span].dev_off + segs[k].span_off;
+          hs_src[k] = segs[k].span == kBounce ? dstage + bounce_base + segs[k].span_off
+                                              : dstage + spans[segs[k].span].dev_off + segs[k].span_off;
           hs_len[k] = segs[k].len;
           hs_off[k] = segs[k].dst_off;
         }
@@ -1343,10 +1382,21 @@ UNZ_EXPORT int infl_buf_batch_iov(const infl_batch_iov_item_t* items, size_t n, 
     rc = run_device_batch_locked(E, flat.data(), n, flags, res.data());
     if (rc != UNZ_OK) return rc;
     if (!dev_ptrs) {
-      for (size_t i = 0; i < n; i++)
-        if (res[i].outlen)
-          CU_TRY(cudaMemcpyAsync(items[i].dst, dout + out_off[i], res[i].outlen, cudaMemcpyDeviceToHost, st), "D2H output");
-      CU_TRY(cudaStreamSynchronize(st), "D2H output");
+      // the group is decoded (run_device_batch_locked returned its results): its bytes go home on the copy stream,
+      // neighbours in host memory as one copy
+      size_t i = 0;
+      while (i < n) {
+        size_t j = i;
+        uint8_t* h0 = static_cast<uint8_t*>(items[i].dst);
+        size_t   len = res[i].outlen;
+        while (j + 1 < n && res[j].outlen == items[j].dstlen && out_off[j + 1] == out_off[j] + items[j].dstlen &&
+               static_cast<uint8_t*>(items[j + 1].dst) == static_cast<uint8_t*>(items[j].dst) + items[j].dstlen) {
+          j++;
+          len = (size_t)(static_cast<uint8_t*>(items[j].dst) - h0) + res[j].outlen;
+        }
+        if (len) CU_TRY(cudaMemcpyAsync(h0, dout + out_off[i], len, cudaMemcpyDeviceToHost, E->stream3), "D2H output");
+        i = j + 1;
+      }
     }
   }
   for (size_t i = 0; i < n; i++) {
@@ -1358,6 +1408,40 @@ UNZ_EXPORT int infl_buf_batch_iov(const infl_batch_iov_item_t* items, size_t n, 
     }
   }
   return UNZ_OK;
+}
+
+UNZ_EXPORT int infl_buf_batch_iov(const infl_batch_iov_item_t* items, size_t n, int flags,
+                                  infl_batch_result_t* results) {
+  if (n == 0) return UNZ_OK;
+  if (!items || !results) return fail("null argument");
+  Engine* E = nullptr;
+  if (engine_for_current_device(&E) != UNZ_OK) return UNZ_ERR;
+  std::lock_guard<std::mutex> guard(E->mu);
+  const bool dev_ptrs = (flags & INFL_BATCH_DEVICE_PTRS) != 0;
+  if (dev_ptrs) return iov_group(E, items, n, flags, results, 0);
+  // host pieces: groups of about equal output; while group g decodes, group g - 1 is on its way home
+  std::vector<size_t> obase(n + 1, 0);
+  for (size_t i = 0; i < n; i++) {
+    if (items[i].dstlen > 0xFFFFFFFFull) return fail("stream larger than 4 GiB - 1 (the reference API limit)");
+    obase[i + 1] = align_up(obase[i] + items[i].dstlen);
+  }
+  if (E->d_out.reserve(obase[n] + 64)) return UNZ_ERR;
+  // (a group wants about a GiB of output: the split-point decoder needs thousands of chunks to fill the GPU --
+  //  four groups of 256 MiB took 105 ms where one took 63)
+  const size_t groups = std::min<size_t>(8, std::max<size_t>(1, obase[n] >> 30));
+  int    rc = UNZ_OK;
+  size_t a = 0;
+  for (size_t g = 0; g < groups && rc == UNZ_OK && a < n; g++) {
+    size_t b = a;
+    const size_t upto = g + 1 == groups ? obase[n] : obase[n] / groups * (g + 1);
+    while (b < n && (b == a || obase[b + 1] <= upto)) b++;
+    if (g + 1 == groups) b = n;
+    rc = iov_group(E, items + a, b - a, flags, results + a, obase[a]);
+    a = b;
+  }
+  const cudaError_t e = cudaStreamSynchronize(E->stream3);
+  if (e != cudaSuccess && rc == UNZ_OK) rc = fail("D2H output", e);
+  return rc;
 }
 
 // ---------------------------------------------------------------------------------------------------
@@ -1414,7 +1498,6 @@ struct unz__stream_t {
 namespace {
 
 constexpr size_t kPiecePage      = 1 << 20;
-constexpr size_t kCopyThreshold  = 8192;
 
 void stream_clear_pieces(unz__stream_t* s) {
   s->pieces.clear();

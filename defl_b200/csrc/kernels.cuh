@@ -201,7 +201,21 @@ gather_pieces_kernel(const void* const* __restrict__ seg_src, const uint64_t* __
   const uint32_t lane   = threadIdx.x & 31;
   const uint64_t warp   = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const uint64_t nwarps = ((uint64_t)gridDim.x * blockDim.x) >> 5;
-  for (uint64_t s = warp; s < nseg; s += nwarps) {
+  // pieces are taken 32 at a time.  When all 32 are tiny (a PNG cut into 1-byte IDATs, test_files.c:300-307) every
+  // lane copies one piece by itself; otherwise the warp copies them one after another, 16 bytes per lane and step.
+  for (uint64_t s0 = warp * 32u; s0 < nseg; s0 += nwarps * 32u) {
+    const uint64_t mine = s0 + lane;
+    const uint64_t mylen = mine < nseg ? seg_len[mine] : 0u;
+    if (__all_sync(0xFFFFFFFFu, mylen <= 16u)) {
+      if (mylen) {
+        const uint8_t* src = static_cast<const uint8_t*>(seg_src[mine]);
+        uint8_t*       dst = out + seg_dst_off[mine];
+        for (uint32_t j = 0; j < (uint32_t)mylen; j++) dst[j] = __ldg(src + j);
+      }
+      continue;
+    }
+   const uint64_t s1 = s0 + 32u < nseg ? s0 + 32u : nseg;
+   for (uint64_t s = s0; s < s1; s++) {
     const uint8_t* src = static_cast<const uint8_t*>(seg_src[s]);
     uint8_t*       dst = out + seg_dst_off[s];
     uint64_t       n   = seg_len[s];
@@ -237,6 +251,7 @@ gather_pieces_kernel(const void* const* __restrict__ seg_src, const uint64_t* __
       }
     }
     for (uint64_t j = (nvec << 4) + lane; j < n; j += 32) dst[j] = __ldg(src + j);
+   }
   }
 }
 

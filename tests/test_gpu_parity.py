@@ -544,3 +544,76 @@ def test_engine4_parity(gpu_lib, corpus, fuzz_ref):
             assert int(g["inpos"]) == len(z) - 4
     finally:
         d.set_engine(3)
+
+
+@pytest.mark.gpu
+def test_chunk_lists_scattered_host_pieces_and_device_pieces(gpu_lib):
+    """infl_buf_batch_iov with pieces that are NOT neighbours in memory: (a) host pieces in separate allocations,
+    handed over in shuffled allocation order (small ones ride the pinned bounce buffer, large ones one DMA each);
+    (b) INFL_BATCH_DEVICE_PTRS with about a million device-resident pieces (1-byte pieces included), so
+    gather_pieces_kernel sees real descriptor counts.  Reference semantics: the stream is the concatenation of the
+    pieces in call order (mem.c:114-216)."""
+    import torch
+    from defl_b200 import synth, api
+    d = gpu_lib
+    Z = zlib.Z_DEFAULT_STRATEGY
+    streams = synth.make_streams([("text", 300000, 61, 6, Z), ("png", 200000, 62, 6, Z), ("log", 250000, 63, 9, Z),
+                                  ("rand", 50000, 64, 6, Z)], threads=2)
+    rng = np.random.default_rng(12)
+    # (a) host: every piece its own numpy allocation, created in random order so that neighbours in the stream are
+    # not neighbours on the heap
+    piece_lists = []
+    for raw, z in streams:
+        cuts, at = [], 0
+        while at < len(z):
+            n = int(rng.choice([1, 3, 17, 200, 5000, 9000, 40000]))
+            cuts.append((at, min(n, len(z) - at)))
+            at += n
+        order = rng.permutation(len(cuts))
+        bufs = [None] * len(cuts)
+        for j in order:
+            a, n = cuts[j]
+            bufs[j] = np.frombuffer(z[a:a + n], dtype=np.uint8).copy()
+        piece_lists.append(bufs)
+    res, outs = d.infl_buf_batch_iov(piece_lists, [len(r) for r, _ in streams], d.INFL_ZLIB | d.INFL_BATCH_VERIFY_ADLER)
+    for (raw, z), g, out in zip(streams, res, outs):
+        assert int(g["code"]) == 0 and bytes(out) == raw, int(g["info"]) >> 8
+        assert int(g["inpos"]) == len(z) - 4
+    # (b) device pieces: stream 0 and 2 as 1-byte pieces (about 215 000), stream 1 and 3 as 1..64-byte pieces
+    dev = torch.device("cuda", 0)
+    keep, items, caps = [], np.zeros(len(streams), dtype=api.IOV_ITEM_DTYPE), []
+    total_pieces = 0
+    reps = 7                                                      # the same four streams seven times: > 10^6 pieces
+    items = np.zeros(len(streams) * reps, dtype=api.IOV_ITEM_DTYPE)
+    dsts = []
+    for r in range(reps):
+        for i, (raw, z) in enumerate(streams):
+            t = torch.frombuffer(bytearray(z), dtype=torch.uint8).to(dev)
+            if i % 2 == 0:
+                sizes = np.ones(len(z), dtype=np.int64)
+            else:
+                sizes = []
+                left = len(z)
+                while left:
+                    n = min(left, int(rng.integers(1, 65)))
+                    sizes.append(n)
+                    left -= n
+                sizes = np.array(sizes, dtype=np.int64)
+            iov = np.zeros(len(sizes), dtype=api.IOVEC_DTYPE)
+            iov["ptr"] = t.data_ptr() + np.concatenate([[0], np.cumsum(sizes)])[:-1]
+            iov["len"] = sizes
+            dst = torch.zeros(len(raw) + 8, dtype=torch.uint8, device=dev)
+            keep += [t, iov]
+            dsts.append(dst)
+            items[r * len(streams) + i] = (iov.ctypes.data, len(sizes), dst.data_ptr(), len(raw))
+            total_pieces += len(sizes)
+    assert total_pieces > 1_000_000
+    results = np.zeros(len(items), dtype=d.RESULT_DTYPE)
+    rc = d.lib().infl_buf_batch_iov(items.ctypes.data, len(items), int(d.INFL_ZLIB | d.INFL_BATCH_VERIFY_ADLER | d.INFL_BATCH_DEVICE_PTRS),
+                                    results.ctypes.data)
+    assert rc == 0, d.last_error()
+    torch.cuda.synchronize()
+    for k, g in enumerate(results):
+        raw = streams[k % len(streams)][0]
+        assert int(g["code"]) == 0 and int(g["outlen"]) == len(raw), (k, int(g["info"]) >> 8)
+        assert dsts[k][: len(raw)].cpu().numpy().tobytes() == raw, k
