@@ -826,7 +826,7 @@ def main():
             workloads["single_1gib_one_history"] = run_single(
                 args, d, dev, stream=single_history_stream(1 << 30), steps=3,
                 what="configs[3]: one 1 GiB zlib stream of text from ONE deflate() history (level 6, no flush points)")
-            workloads["chunks"] = run_chunks(args, d, dev, nstreams=64, steps=2)
+            workloads["chunks"] = run_chunks(args, d, dev, nstreams=256, steps=2)
 
     if rank == 0:
         line = {
