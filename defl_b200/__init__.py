@@ -14,4 +14,7 @@ from .api import (  # noqa: F401
     lib, infl_buf, infl_buf_batch, infl_buf_batch_iov, InflStream, DeviceBatch, batch_partition,
     last_error, engine_info, kernel_launch_count, set_lanes_per_stream, set_pipeline_shape, set_engine,
     EXPORTED_SYMBOLS,
+    INFL_WRAP_VERIFY, INFL_WRAP_INFO_CRC_MATCH, INFL_WRAP_INFO_BAD_HEADER, INFL_WRAP_INFO_INTERLACED,
+    INFL_WRAP_INFO_BAD_FILTER, GZIP_RESULT_DTYPE, PNG_ITEM_DTYPE, PNG_RESULT_DTYPE,
+    gzip_batch, gzip_batch_raw, crc32_batch, png_batch, png_batch_raw,
 )

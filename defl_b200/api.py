@@ -40,6 +40,7 @@ EXPORTED_SYMBOLS = [
     "infl_batch_partition",
     "infl_device_count", "infl_last_error", "infl_engine_info",
     "infl_kernel_launch_count", "infl_set_lanes_per_stream", "infl_set_pipeline_shape", "infl_set_engine",
+    "infl_gzip_batch", "infl_crc32_batch", "infl_png_batch", "infl_png_unfilter_device",
 ]
 
 _lib = None
@@ -317,3 +318,70 @@ class DeviceBatch:
 
     def results_host(self):
         return self.results.cpu().numpy().view(RESULT_DTYPE).reshape(-1)
+
+
+# ---- include/defl/infl_wrap.h ------------------------------------------------------------------------------
+INFL_WRAP_VERIFY = 0x1000
+INFL_WRAP_INFO_CRC_MATCH, INFL_WRAP_INFO_BAD_HEADER = 0x10, 0x20
+INFL_WRAP_INFO_INTERLACED, INFL_WRAP_INFO_BAD_FILTER = 0x40, 0x80
+GZIP_RESULT_DTYPE = np.dtype([("code", "<i4"), ("crc32", "<u4"), ("outlen", "<u8"), ("inpos", "<u8"),
+                              ("crc32_stored", "<u4"), ("isize_stored", "<u4"), ("info", "<u4"), ("pad", "<u4")])
+PNG_ITEM_DTYPE = np.dtype([("png", "<u8"), ("pnglen", "<u8"), ("pixels", "<u8"), ("pixcap", "<u8")])
+PNG_RESULT_DTYPE = np.dtype([("code", "<i4"), ("width", "<u4"), ("height", "<u4"), ("bit_depth", "u1"),
+                             ("color_type", "u1"), ("interlace", "u1"), ("bpp", "u1"), ("stride", "<u4"),
+                             ("nidat", "<u4"), ("outlen", "<u8"), ("info", "<u4"), ("pad", "<u4")])
+assert GZIP_RESULT_DTYPE.itemsize == 40 and PNG_ITEM_DTYPE.itemsize == 32 and PNG_RESULT_DTYPE.itemsize == 40
+
+
+def gzip_batch_raw(items, flags, results):
+    """items: ITEM_DTYPE array (host or device pointers), results: GZIP_RESULT_DTYPE array."""
+    rc = lib().infl_gzip_batch(ctypes.c_void_p(items.ctypes.data), ctypes.c_size_t(len(items)), ctypes.c_int(int(flags)),
+                               ctypes.c_void_p(results.ctypes.data))
+    if rc != UNZ_OK:
+        raise RuntimeError("infl_gzip_batch: " + last_error())
+
+
+def gzip_batch(members, dstlens, flags=0):
+    """Host gzip members -> (results, [output arrays])."""
+    n = len(members)
+    keep = [_as_u8(m) for m in members]
+    outs = [np.zeros(max(int(d), 1), dtype=np.uint8) for d in dstlens]
+    items = np.zeros(n, dtype=ITEM_DTYPE)
+    for i in range(n):
+        items[i] = (keep[i].ctypes.data if keep[i].size else 0, keep[i].size, outs[i].ctypes.data, int(dstlens[i]))
+    res = np.zeros(n, dtype=GZIP_RESULT_DTYPE)
+    gzip_batch_raw(items, flags, res)
+    return res, [o[: int(r["outlen"])] for o, r in zip(outs, res)]
+
+
+def crc32_batch(buffers):
+    n = len(buffers)
+    keep = [_as_u8(b) for b in buffers]
+    items = np.zeros(n, dtype=ITEM_DTYPE)
+    for i in range(n):
+        items[i] = (keep[i].ctypes.data if keep[i].size else 0, keep[i].size, 0, 0)
+    crc = np.zeros(n, dtype=np.uint32)
+    rc = lib().infl_crc32_batch(ctypes.c_void_p(items.ctypes.data), ctypes.c_size_t(n), ctypes.c_int(0), ctypes.c_void_p(crc.ctypes.data))
+    if rc != UNZ_OK:
+        raise RuntimeError("infl_crc32_batch: " + last_error())
+    return crc
+
+
+def png_batch_raw(items, flags, results):
+    rc = lib().infl_png_batch(ctypes.c_void_p(items.ctypes.data), ctypes.c_size_t(len(items)), ctypes.c_int(int(flags)),
+                              ctypes.c_void_p(results.ctypes.data))
+    if rc != UNZ_OK:
+        raise RuntimeError("infl_png_batch: " + last_error())
+
+
+def png_batch(files, pixcaps, flags=0):
+    """Host PNG files -> (results, [pixel arrays of height * stride bytes])."""
+    n = len(files)
+    keep = [_as_u8(f) for f in files]
+    outs = [np.zeros(max(int(c), 1), dtype=np.uint8) for c in pixcaps]
+    items = np.zeros(n, dtype=PNG_ITEM_DTYPE)
+    for i in range(n):
+        items[i] = (keep[i].ctypes.data if keep[i].size else 0, keep[i].size, outs[i].ctypes.data, int(pixcaps[i]))
+    res = np.zeros(n, dtype=PNG_RESULT_DTYPE)
+    png_batch_raw(items, flags, res)
+    return res, [o[: int(r["outlen"])] for o, r in zip(outs, res)]

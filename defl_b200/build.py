@@ -7,8 +7,8 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libdefl_b200.so")
 SOURCES = ["defl_b200.cu"]
-DEPS = sorted(f for f in os.listdir(CSRC) if f.endswith((".cu", ".cuh"))) + \
-       ["../../include/defl/infl.h", "../../include/defl/infl_batch.h", "../../include/defl/common.h"]
+DEPS = sorted(f for f in os.listdir(CSRC) if f.endswith((".cu", ".cuh", ".inc"))) + \
+       ["../../include/defl/infl.h", "../../include/defl/infl_batch.h", "../../include/defl/common.h", "../../include/defl/infl_wrap.h"]
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",

@@ -25,6 +25,8 @@
 #include "../../include/defl/infl_batch.h"
 #include "../../include/defl/version.h"
 #include "kernels.cuh"
+#include "wrap_kernels.cuh"
+#include "../../include/defl/infl_wrap.h"
 
 namespace {
 
@@ -1738,3 +1740,5 @@ UNZ_EXPORT int infl_stream(infl_stream_t* s, const void* src, uint32_t srclen) {
 }
 
 }  // extern "C"
+
+#include "wrap_host.inc"

@@ -11,7 +11,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 def _declared():
     names = []
-    for h in ("infl.h", "infl_batch.h"):
+    for h in ("infl.h", "infl_batch.h", "infl_wrap.h"):
         src = open(os.path.join(ROOT, "include", "defl", h)).read()
         names += re.findall(r"UNZ_EXPORT\s+[\w\s\*]+?\b(infl\w*)\s*\(", src)
     return sorted(set(names))
