@@ -16,6 +16,7 @@ batch of the same shape (streams shard with no collective) -> weak
 reference could not be compiled) on the same workload shape with all host threads.
 """
 import argparse
+import ctypes
 import json
 import os
 import sys
@@ -50,7 +51,7 @@ def parse():
     ap.add_argument("--chunk-streams", type=int, default=256, help="chunks workload: 4 MiB streams per step")
     ap.add_argument("--sharded-pool-mib", type=int, default=512, help="mixed_sharded sub-record: distinct MiB generated on the host")
     ap.add_argument("--no-extra", action="store_true", help="headline only: skip the workloads sub-records")
-    ap.add_argument("--workload", default="batch", choices=["batch", "single", "mixed", "chunks", "sharded"],
+    ap.add_argument("--workload", default="batch", choices=["batch", "single", "mixed", "chunks", "sharded", "wrap"],
                     help="batch = configs[1] (headline); single = configs[3], one large stream, split-point decode")
     ap.add_argument("--single-bytes", type=int, default=1 << 30)
     ap.add_argument("--e2e-steps", type=int, default=2)
@@ -489,6 +490,135 @@ def run_mixed_sharded(args, d, dev, rank, world, local, dist, per_gpu_gib=None, 
         "gpu_launches": int(launches)}
 
 
+def run_wrap(args, d, dev):
+    """The rows either side of the hot path (include/defl/infl_wrap.h), device resident: CRC-32 of one
+    large buffer, the PNG scanline un-filter on a batch of RGBA images, whole PNG files (container walk + IDAT
+    gather + inflate + un-filter) and gzip members.  Every result is compared with the CPU oracle
+    (oracle/wrap_oracle.c) or the generator's bytes; the oracle is also the CPU figure beside each number."""
+    import torch
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import wrap_lib as wl
+    from defl_b200 import synth, api
+    peak, peak_src = peaks()
+    rec = {}
+    rng = np.random.default_rng(1)
+
+    def timed(fn, reps=3):
+        fn()
+        torch.cuda.synchronize()
+        ts = []
+        for _ in range(reps):
+            t = time.perf_counter(); fn(); torch.cuda.synchronize(); ts.append(time.perf_counter() - t)
+        return float(np.mean(ts))
+
+    # -- CRC-32 of one 1 GiB buffer
+    nb = 1 << 30
+    t_buf = torch.randint(0, 256, (nb,), dtype=torch.uint8, device=dev)
+    items = np.zeros(1, dtype=d.ITEM_DTYPE)
+    items[0] = (t_buf.data_ptr(), nb, 0, 0)
+    crc = np.zeros(1, dtype=np.uint32)
+    call = lambda: d.lib().infl_crc32_batch(items.ctypes.data, 1, int(d.INFL_BATCH_DEVICE_PTRS), crc.ctypes.data)
+    dt = timed(call)
+    sample = t_buf[: 64 << 20].cpu().numpy().tobytes()
+    t0 = time.perf_counter(); want = wl.crc32(sample); cpu_dt = time.perf_counter() - t0
+    items[0] = (t_buf.data_ptr(), len(sample), 0, 0)
+    call()
+    assert int(crc[0]) == want == (zlib.crc32(sample) & 0xFFFFFFFF)
+    rec["crc32"] = {"value": nb / dt / 1e9, "unit": "GB/s", "bytes": nb, "ms": dt * 1e3, "byte_exact": True,
+                    "roofline": {"bound": "hbm", "achieved": nb / dt / 1e9, "peak": peak, "frac": nb / dt / 1e9 / peak,
+                                 "algorithmic_bytes": "1 read per byte"},
+                    "cpu_baseline": {"value": len(sample) / cpu_dt / 1e9, "unit": "GB/s", "cores": 1, "kind": "port",
+                                     "sample": "64 MiB, oracle/wrap_oracle.c (bit at a time, RFC 1952 section 8)"}}
+    del t_buf
+
+    # -- PNG: 2048 RGBA images of 256 x 256 (smooth content, all five filter types), as scanline data and as files
+    w = h = 256
+    uniq = 32
+    imgs = []
+    for k in range(uniq):
+        x = np.arange(h * w * 4)
+        pix = ((x // 4 * (3 + k) + x % 4 * 31 + rng.integers(0, 3, x.size)) & 255).astype(np.uint8).tobytes()
+        f, stride, bpp = wl.png_file(w, h, 8, 6, pix, ftypes=(4, 1, 2, 3, 0), idat=8192)
+        imgs.append((f, pix, wl.png_filter_rows(pix, h, stride, bpp, (4, 1, 2, 3, 0))))
+    n = 2048
+    stride, bpp = w * 4, 4
+    rawlen, pixlen = h * (stride + 1), h * stride
+    t_raw = torch.cat([torch.frombuffer(bytearray(imgs[i % uniq][2]), dtype=torch.uint8) for i in range(n)]).to(dev)
+    t_pix = torch.zeros(n * pixlen, dtype=torch.uint8, device=dev)
+    P = ctypes.c_void_p * n
+    raws = P(*[t_raw.data_ptr() + i * rawlen for i in range(n)])
+    pixs = P(*[t_pix.data_ptr() + i * pixlen for i in range(n)])
+    hh = np.full(n, h, dtype=np.uint32); ss = np.full(n, stride, dtype=np.uint32); bb = np.full(n, bpp, dtype=np.uint32)
+    bad = np.zeros(n, dtype=np.uint32)
+    call = lambda: d.lib().infl_png_unfilter_device(raws, pixs, hh.ctypes.data, ss.ctypes.data, bb.ctypes.data, n,
+                                                    bad.ctypes.data, None)
+    dt = timed(call)
+    host = t_pix.cpu().numpy()
+    for i in (0, 1, uniq - 1, n - 1):
+        assert host[i * pixlen:(i + 1) * pixlen].tobytes() == imgs[i % uniq][1], "un-filtered pixels differ"
+    t0 = time.perf_counter()
+    for k in range(uniq):
+        assert wl.png_unfilter(imgs[k][2], h, stride, bpp)[1] == imgs[k][1]
+    cpu_dt = time.perf_counter() - t0
+    alg = n * (rawlen + pixlen)
+    rec["png_unfilter"] = {"value": n * pixlen / dt / 1e9, "unit": "GB/s of pixels", "images": n, "image": f"{w}x{h} RGBA8", "ms": dt * 1e3,
+                           "byte_exact": True,
+                           "roofline": {"bound": "hbm", "achieved": alg / dt / 1e9, "peak": peak, "frac": alg / dt / 1e9 / peak,
+                                        "algorithmic_bytes": "scanline data in + pixels out"},
+                           "cpu_baseline": {"value": uniq * pixlen / cpu_dt / 1e9, "unit": "GB/s of pixels", "cores": 1, "kind": "port",
+                                            "sample": f"{uniq} images, oracle/wrap_oracle.c"}}
+    del t_raw
+    # whole files, device resident
+    blob = b"".join(f for f, _, _ in imgs)
+    offs = np.concatenate([[0], np.cumsum([len(f) for f, _, _ in imgs])])
+    t_files = torch.frombuffer(bytearray(blob), dtype=torch.uint8).to(dev)
+    t_pix.zero_()
+    pitems = np.zeros(n, dtype=d.PNG_ITEM_DTYPE)
+    for i in range(n):
+        k = i % uniq
+        pitems[i] = (t_files.data_ptr() + int(offs[k]), len(imgs[k][0]), t_pix.data_ptr() + i * pixlen, pixlen)
+    pres = np.zeros(n, dtype=d.PNG_RESULT_DTYPE)
+    call = lambda: d.png_batch_raw(pitems, d.INFL_WRAP_VERIFY | d.INFL_BATCH_DEVICE_PTRS, pres)
+    l0 = d.kernel_launch_count()
+    dt = timed(call)
+    launches = (d.kernel_launch_count() - l0) // 4
+    assert (pres["code"] == 0).all()
+    host = t_pix.cpu().numpy()
+    for i in (0, 5, n - 1):
+        assert host[i * pixlen:(i + 1) * pixlen].tobytes() == imgs[i % uniq][1], "decoded PNG differs"
+    t0 = time.perf_counter()
+    for k in range(uniq):
+        assert wl.png_decode(imgs[k][0])[1] == imgs[k][1]
+    cpu_dt = time.perf_counter() - t0
+    fbytes = sum(len(imgs[i % uniq][0]) for i in range(n))
+    rec["png_files"] = {"value": n / dt, "unit": "images/s", "pixel_GBps": n * pixlen / dt / 1e9, "images": n, "ms": dt * 1e3,
+                        "file_bytes": fbytes, "idat_per_file": int(pres["nidat"][0]), "launches_per_call": int(launches), "byte_exact": True,
+                        "cpu_baseline": {"value": uniq / cpu_dt, "unit": "images/s", "cores": 1, "kind": "port",
+                                         "sample": f"{uniq} files: oracle walk + Python zlib + oracle un-filter"}}
+    del t_files, t_pix
+    # -- gzip members: 20 000 x 64 KiB text
+    pool = [synth.payload("text", 65536, 300 + i) for i in range(256)]
+    mem = [wl.gzip_member(r, name=b"f%d.txt" % i) for i, r in enumerate(pool)]
+    src_h, so, sl = synth.pack(mem, align=16)
+    ng = 20000
+    t_src = torch.from_numpy(src_h).to(dev)
+    t_dst = torch.zeros(ng * 65536, dtype=torch.uint8, device=dev)
+    gitems = np.zeros(ng, dtype=d.ITEM_DTYPE)
+    k = np.arange(ng)
+    gitems["src"] = t_src.data_ptr() + so[k % 256]
+    gitems["srclen"] = sl[k % 256]
+    gitems["dst"] = t_dst.data_ptr() + k * 65536
+    gitems["dstlen"] = 65536
+    gres = np.zeros(ng, dtype=d.GZIP_RESULT_DTYPE)
+    call = lambda: d.gzip_batch_raw(gitems, d.INFL_WRAP_VERIFY | d.INFL_BATCH_DEVICE_PTRS, gres)
+    dt = timed(call)
+    assert (gres["code"] == 0).all() and (gres["crc32"] == gres["crc32_stored"]).all()
+    assert t_dst[:65536].cpu().numpy().tobytes() == pool[0]
+    rec["gzip_members"] = {"value": ng * 65536 / dt / 1e9, "unit": "GB/s decompressed", "members": ng, "ms": dt * 1e3, "byte_exact": True,
+                           "note": "header parse kernel + batch inflate + CRC-32 kernel + host combination of the 64 KiB partial CRCs"}
+    return rec
+
+
 def run_mixed(args, d, dev, rank, world, local, dist):
     """BASELINE.json configs[4] shape: stored / fixed / dynamic blocks, levels 1/6/9, sizes log-uniform in
     [64 KiB, 4 MiB], classes text/log/png/rand/zero (synth.config5_specs).  Each GPU owns --mixed-gib GiB of
@@ -651,6 +781,9 @@ def main():
         return
     if args.workload == "chunks":
         print(json.dumps(run_chunks(args, d, dev)))
+        return
+    if args.workload == "wrap":
+        print(json.dumps(run_wrap(args, d, dev)))
         return
     if args.workload == "sharded":
         rec = run_mixed_sharded(args, d, dev, rank, world, local, dist)
@@ -827,6 +960,7 @@ def main():
                 args, d, dev, stream=single_history_stream(1 << 30), steps=3,
                 what="configs[3]: one 1 GiB zlib stream of text from ONE deflate() history (level 6, no flush points)")
             workloads["chunks"] = run_chunks(args, d, dev, nstreams=256, steps=2)
+            workloads["wrap"] = run_wrap(args, d, dev)
 
     if rank == 0:
         line = {
