@@ -16,5 +16,5 @@ from .api import (  # noqa: F401
     EXPORTED_SYMBOLS,
     INFL_WRAP_VERIFY, INFL_WRAP_INFO_CRC_MATCH, INFL_WRAP_INFO_BAD_HEADER, INFL_WRAP_INFO_INTERLACED,
     INFL_WRAP_INFO_BAD_FILTER, GZIP_RESULT_DTYPE, PNG_ITEM_DTYPE, PNG_RESULT_DTYPE,
-    gzip_batch, gzip_batch_raw, crc32_batch, png_batch, png_batch_raw,
+    gzip_batch, gzip_batch_raw, crc32_batch, png_batch, png_batch_raw, ZIP_ENTRY_DTYPE, zip_list, zip_extract,
 )

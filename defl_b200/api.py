@@ -40,7 +40,7 @@ EXPORTED_SYMBOLS = [
     "infl_batch_partition",
     "infl_device_count", "infl_last_error", "infl_engine_info",
     "infl_kernel_launch_count", "infl_set_lanes_per_stream", "infl_set_pipeline_shape", "infl_set_engine",
-    "infl_gzip_batch", "infl_crc32_batch", "infl_png_batch", "infl_png_unfilter_device",
+    "infl_gzip_batch", "infl_crc32_batch", "infl_png_batch", "infl_png_unfilter_device", "infl_zip_list", "infl_zip_extract",
 ]
 
 _lib = None
@@ -384,4 +384,37 @@ def png_batch(files, pixcaps, flags=0):
         items[i] = (keep[i].ctypes.data if keep[i].size else 0, keep[i].size, outs[i].ctypes.data, int(pixcaps[i]))
     res = np.zeros(n, dtype=PNG_RESULT_DTYPE)
     png_batch_raw(items, flags, res)
+    return res, [o[: int(r["outlen"])] for o, r in zip(outs, res)]
+
+
+ZIP_ENTRY_DTYPE = np.dtype([("local_off", "<u8"), ("data_off", "<u8"), ("csize", "<u8"), ("usize", "<u8"), ("crc32", "<u4"),
+                            ("method", "<u2"), ("gpflags", "<u2"), ("name_off", "<u4"), ("name_len", "<u2"), ("ok", "<u2")])
+assert ZIP_ENTRY_DTYPE.itemsize == 48
+
+
+def zip_list(archive, cap=65536):
+    """Host archive bytes -> (entries[ZIP_ENTRY_DTYPE], names)."""
+    a = _as_u8(archive)
+    ent = np.zeros(cap, dtype=ZIP_ENTRY_DTYPE)
+    cnt = ctypes.c_size_t()
+    rc = lib().infl_zip_list(ctypes.c_void_p(a.ctypes.data), ctypes.c_uint64(a.size), ctypes.c_int(0), ctypes.c_void_p(ent.ctypes.data),
+                             ctypes.c_size_t(cap), ctypes.byref(cnt))
+    if rc != UNZ_OK:
+        raise RuntimeError("infl_zip_list: " + last_error())
+    ent = ent[: min(cnt.value, cap)]
+    names = [bytes(a[int(e["name_off"]): int(e["name_off"]) + int(e["name_len"])]) for e in ent]
+    return ent, names
+
+
+def zip_extract(archive, entries, flags=0):
+    a = _as_u8(archive)
+    n = len(entries)
+    outs = [np.zeros(max(int(e["usize"]), 1), dtype=np.uint8) for e in entries]
+    ptrs = (ctypes.c_void_p * n)(*[o.ctypes.data for o in outs])
+    ent = np.ascontiguousarray(entries)
+    res = np.zeros(n, dtype=GZIP_RESULT_DTYPE)
+    rc = lib().infl_zip_extract(ctypes.c_void_p(a.ctypes.data), ctypes.c_uint64(a.size), ctypes.c_void_p(ent.ctypes.data), ctypes.c_size_t(n),
+                                ptrs, ctypes.c_int(int(flags)), ctypes.c_void_p(res.ctypes.data))
+    if rc != UNZ_OK:
+        raise RuntimeError("infl_zip_extract: " + last_error())
     return res, [o[: int(r["outlen"])] for o, r in zip(outs, res)]

@@ -118,6 +118,67 @@ __global__ void gzip_header_kernel(const uint8_t* const* __restrict__ src, const
   if (i < n) out[i] = gzip_parse(src[i], len[i]);
 }
 
+// ---- ZIP archives (APPNOTE 4.3: end of central directory, central file headers, local file headers) ------------
+// One thread walks the central directory of an archive that lives on the device and fills one record per member.
+struct ZipEntry {
+  uint64_t local_off;     // offset of the local file header
+  uint64_t data_off;      // offset of the member's (compressed) data
+  uint64_t csize, usize;
+  uint32_t crc32;
+  uint16_t method;        // 0 stored, 8 deflate
+  uint16_t gpflags;
+  uint32_t name_off;      // of the name inside the archive (central directory copy)
+  uint16_t name_len;
+  uint16_t ok;            // 1: a member this path can extract (method 0 / 8, not encrypted, no ZIP64 sizes)
+};
+
+__device__ __forceinline__ uint32_t le16(const uint8_t* p) { return p[0] | ((uint32_t)p[1] << 8); }
+__device__ __forceinline__ uint32_t le32(const uint8_t* p) { return le16(p) | (le16(p + 2) << 16); }
+
+// out[0].. up to cap entries; *count = members in the directory (may exceed cap), or 0xFFFFFFFF when no directory
+__global__ void zip_walk_kernel(const uint8_t* __restrict__ z, uint64_t n, ZipEntry* __restrict__ out, uint32_t cap,
+                                uint32_t* __restrict__ count) {
+  if (blockIdx.x || threadIdx.x) return;
+  *count = 0xFFFFFFFFu;
+  if (n < 22) return;
+  uint64_t e = n - 22;                                      // end of central directory record: scan back over the comment
+  const uint64_t stop = n > 22 + 65535 ? n - 22 - 65535 : 0;
+  for (;; e--) {
+    if (le32(z + e) == 0x06054B50u && e + 22 + le16(z + e + 20) <= n) break;
+    if (e == stop) return;
+  }
+  const uint32_t total = le16(z + e + 10), cdsize = le32(z + e + 12), cdoff = le32(z + e + 16);
+  if (total == 0xFFFFu || cdoff == 0xFFFFFFFFu || (uint64_t)cdoff + cdsize > e) return;     // ZIP64: not here
+  uint64_t at = cdoff;
+  uint32_t k = 0;
+  for (; k < total; k++) {
+    if (at + 46 > e || le32(z + at) != 0x02014B50u) return;
+    const uint32_t nl = le16(z + at + 28), xl = le16(z + at + 30), cl = le16(z + at + 32);
+    if (k < cap) {
+      ZipEntry r;
+      r.gpflags = (uint16_t)le16(z + at + 8); r.method = (uint16_t)le16(z + at + 10);
+      r.crc32 = le32(z + at + 16); r.csize = le32(z + at + 20); r.usize = le32(z + at + 24);
+      r.local_off = le32(z + at + 42);
+      r.name_off = (uint32_t)(at + 46); r.name_len = (uint16_t)nl;
+      r.data_off = 0;
+      bool ok = (r.method == 0 || r.method == 8) && !(r.gpflags & 1u) && r.csize != 0xFFFFFFFFu && r.usize != 0xFFFFFFFFu &&
+                r.local_off != 0xFFFFFFFFu;
+      if (ok) {
+        const uint64_t lo = r.local_off;
+        ok = lo + 30 <= n && le32(z + lo) == 0x04034B50u;
+        if (ok) {
+          r.data_off = lo + 30 + le16(z + lo + 26) + le16(z + lo + 28);
+          ok = r.data_off + r.csize <= n;
+        }
+      }
+      r.ok = ok ? 1 : 0;
+      out[k] = r;
+    }
+    at += 46 + (uint64_t)nl + xl + cl;
+  }
+  *count = total;
+}
+
 // ---- PNG container walk (PNG spec 5.3; the reference's motivating caller, README.md:120-155) ---------------------
 // One thread per file: check the signature, read IHDR, and list the IDAT chunks' payloads as gather descriptors
 // (pointer, length, offset in the joined zlib stream) -- the host never touches the file's bytes.

@@ -46,6 +46,30 @@ UNZ_EXPORT int infl_gzip_batch(const infl_batch_item_t *items, size_t n, int fla
 /* crc[i] = CRC-32 of items[i].src[0..srclen) (dst, dstlen ignored). */
 UNZ_EXPORT int infl_crc32_batch(const infl_batch_item_t *items, size_t n, int flags, uint32_t *crc);
 
+/* ---- ZIP archives (PKWARE APPNOTE 4.3; the `unz` caller) ------------------------------------------------------ */
+typedef struct infl_zip_entry_t {
+  uint64_t local_off;      /* offset of the local file header                                  */
+  uint64_t data_off;       /* offset of the member's data                                      */
+  uint64_t csize, usize;   /* compressed / uncompressed size (central directory)               */
+  uint32_t crc32;
+  uint16_t method;         /* 0 stored, 8 deflate                                              */
+  uint16_t gpflags;
+  uint32_t name_off;       /* of the file name inside the archive                              */
+  uint16_t name_len;
+  uint16_t ok;             /* 1: extractable here (method 0 / 8, not encrypted, no ZIP64 sizes) */
+} infl_zip_entry_t;
+
+/* Walk the central directory on the device.  entries[0..min(*count, cap)) are filled; *count = members in the
+   archive.  UNZ_ERR when there is no (non-ZIP64) end-of-central-directory record. */
+UNZ_EXPORT int infl_zip_list(const void *zip, uint64_t ziplen, int flags, infl_zip_entry_t *entries, size_t cap,
+                             size_t *count);
+
+/* Extract n members: entries[i] -> dst[i][0..entries[i].usize).  Deflated members go through the batch engine,
+   stored ones are copied; CRC-32 is computed on the device and compared (results[i].crc32 / crc32_stored;
+   INFL_WRAP_VERIFY makes a mismatch UNZ_ERR).  isize_stored receives the directory's uncompressed size. */
+UNZ_EXPORT int infl_zip_extract(const void *zip, uint64_t ziplen, const infl_zip_entry_t *entries, size_t n,
+                                void *const *dst, int flags, infl_gzip_result_t *results);
+
 typedef struct infl_png_item_t {
   const void *png;         /* the whole file                                                 */
   uint64_t    pnglen;

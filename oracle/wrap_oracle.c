@@ -104,3 +104,46 @@ wrap_oracle_png_idat(const uint8_t *f, uint64_t n, uint32_t *hdr, uint8_t *z, ui
   }
   return (end && *nidat) ? (int64_t)zl : -1;
 }
+
+/* ZIP (PKWARE APPNOTE 4.3): the central directory of an archive.  Fills up to cap records of
+   {local_off, data_off, csize, usize, crc32, method | gpflags << 16, name_off, name_len | ok << 16} (8 x uint64)
+   and returns the number of members, or -1 without a (non-ZIP64) end-of-central-directory record. */
+static uint32_t le16(const uint8_t *p) { return p[0] | ((uint32_t)p[1] << 8); }
+static uint32_t le32(const uint8_t *p) { return le16(p) | (le16(p + 2) << 16); }
+
+int64_t
+wrap_oracle_zip_list(const uint8_t *z, uint64_t n, uint64_t *out, uint32_t cap) {
+  uint64_t e, stop, at;
+  uint32_t total, cdsize, cdoff, k;
+
+  if (n < 22) return -1;
+  e = n - 22;
+  stop = n > 22 + 65535 ? n - 22 - 65535 : 0;
+  for (;; e--) {
+    if (le32(z + e) == 0x06054B50u && e + 22 + le16(z + e + 20) <= n) break;
+    if (e == stop) return -1;
+  }
+  total = le16(z + e + 10); cdsize = le32(z + e + 12); cdoff = le32(z + e + 16);
+  if (total == 0xFFFFu || cdoff == 0xFFFFFFFFu || (uint64_t)cdoff + cdsize > e) return -1;
+  at = cdoff;
+  for (k = 0; k < total; k++) {
+    uint32_t nl, xl, cl;
+    if (at + 46 > e || le32(z + at) != 0x02014B50u) return -1;
+    nl = le16(z + at + 28); xl = le16(z + at + 30); cl = le16(z + at + 32);
+    if (k < cap) {
+      uint64_t *r = out + 8u * k;
+      uint32_t gp = le16(z + at + 8), method = le16(z + at + 10);
+      int      ok;
+      r[0] = le32(z + at + 42); r[1] = 0; r[2] = le32(z + at + 20); r[3] = le32(z + at + 24); r[4] = le32(z + at + 16);
+      r[5] = method | ((uint64_t)gp << 16); r[6] = at + 46;
+      ok = (method == 0 || method == 8) && !(gp & 1u) && r[2] != 0xFFFFFFFFu && r[3] != 0xFFFFFFFFu && r[0] != 0xFFFFFFFFu;
+      if (ok) {
+        ok = r[0] + 30 <= n && le32(z + r[0]) == 0x04034B50u;
+        if (ok) { r[1] = r[0] + 30 + le16(z + r[0] + 26) + le16(z + r[0] + 28); ok = r[1] + r[2] <= n; }
+      }
+      r[7] = nl | ((uint64_t)(ok ? 1 : 0) << 16);
+    }
+    at += 46 + (uint64_t)nl + xl + cl;
+  }
+  return total;
+}

@@ -164,3 +164,29 @@ def test_png_batch_device_resident_many_files(gpu_lib):
     for i in range(0, n, 7):
         want = base[i % 24][1]
         assert host[pixoff[i]: pixoff[i] + len(want)].tobytes() == want, i
+
+
+def test_zip_archives(gpu_lib):
+    import io
+    import zipfile
+    from test_wrap_oracle import _archive
+    d = gpu_lib
+    z, files = _archive()
+    ent, names = d.zip_list(z)
+    want = wl.zip_list(z)
+    assert len(ent) == len(want) == len(files)
+    for e, w_, nm in zip(ent, want, names):
+        for f in ("local_off", "data_off", "csize", "usize", "crc32", "method", "gpflags", "name_off", "name_len", "ok"):
+            assert int(e[f]) == w_[f], f
+    res, outs = d.zip_extract(z, ent, d.INFL_WRAP_VERIFY)
+    zf = zipfile.ZipFile(io.BytesIO(z))
+    for e, nm, g, out in zip(ent, names, res, outs):
+        assert int(g["code"]) == 0 and bytes(out) == zf.read(nm.decode()) == files[nm.decode()], nm
+        assert int(g["crc32"]) == int(e["crc32"]) and int(g["info"]) & d.INFL_WRAP_INFO_CRC_MATCH
+    # a damaged member: its CRC no longer matches (or the body no longer decodes)
+    bad = bytearray(z)
+    bad[int(ent[3]["data_off"]) + 40] ^= 0x20
+    res, outs = d.zip_extract(bytes(bad), ent, d.INFL_WRAP_VERIFY)
+    assert int(res[3]["code"]) != 0 and all(int(res[i]["code"]) == 0 for i in (0, 1, 2, 4))
+    with pytest.raises(RuntimeError):
+        d.zip_list(z[:-30])

@@ -52,3 +52,33 @@ def test_png_unfilter_round_trip_and_walk():
     assert nidat == (len(z) + 36) // 37
     assert wl.png_idat(b"\x89PNG\r\n\x1a\n" + bytes(40))[0] < 0
     assert wl.png_unfilter(bytes([5, 1, 2, 3]), 1, 3, 1)[0] == 1
+
+
+def _archive():
+    import io
+    import zipfile
+    rng = np.random.default_rng(8)
+    files = {"a.txt": b"hello zip\n" * 500, "dir/b.bin": rng.integers(0, 256, 70000, dtype=np.uint8).tobytes(),
+             "empty": b"", "c.log": b"2024-01-01 INFO something happened\n" * 4000, "one": b"x"}
+    buf = io.BytesIO()
+    with zipfile.ZipFile(buf, "w") as z:
+        for i, (name, data) in enumerate(files.items()):
+            z.writestr(zipfile.ZipInfo(name), data, compress_type=zipfile.ZIP_STORED if i == 1 else zipfile.ZIP_DEFLATED)
+        z.comment = b"archive comment"
+    return buf.getvalue(), files
+
+
+def test_zip_directory_against_zipfile():
+    import io
+    import zipfile
+    z, files = _archive()
+    ents = wl.zip_list(z)
+    infos = zipfile.ZipFile(io.BytesIO(z)).infolist()
+    assert len(ents) == len(infos) == len(files)
+    for e, i in zip(ents, infos):
+        assert z[e["name_off"]: e["name_off"] + e["name_len"]].decode() == i.filename
+        assert (e["csize"], e["usize"], e["crc32"], e["method"], e["local_off"]) == (i.compress_size, i.file_size, i.CRC, i.compress_type, i.header_offset)
+        assert e["ok"] == 1
+        data = z[e["data_off"]: e["data_off"] + e["csize"]]
+        assert (zlib.decompress(data, -15) if e["method"] == 8 else data) == files[i.filename]
+    assert wl.zip_list(z[:-5]) is None and wl.zip_list(b"PK" + bytes(40)) is None

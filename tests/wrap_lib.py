@@ -23,6 +23,8 @@ def oracle():
         lib.wrap_oracle_png_unfilter.argtypes = [ctypes.c_char_p, ctypes.c_void_p, ctypes.c_uint32, ctypes.c_uint32, ctypes.c_uint32]
         lib.wrap_oracle_png_idat.restype = ctypes.c_int64
         lib.wrap_oracle_png_idat.argtypes = [ctypes.c_char_p, ctypes.c_uint64, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_uint64, ctypes.c_void_p]
+        lib.wrap_oracle_zip_list.restype = ctypes.c_int64
+        lib.wrap_oracle_zip_list.argtypes = [ctypes.c_char_p, ctypes.c_uint64, ctypes.c_void_p, ctypes.c_uint32]
         _o = lib
     return _o
 
@@ -70,6 +72,20 @@ def png_decode(f):
         return -1, b"", hdr
     rc, pix = png_unfilter(raw, h, stride, bpp)
     return (-1 if rc else 0), pix, hdr
+
+
+def zip_list(z, cap=4096):
+    """-> list of dicts (the oracle's walk of the central directory), or None."""
+    out = (ctypes.c_uint64 * (8 * cap))()
+    n = oracle().wrap_oracle_zip_list(bytes(z), len(z), out, cap)
+    if n < 0:
+        return None
+    ents = []
+    for k in range(min(n, cap)):
+        r = out[8 * k: 8 * k + 8]
+        ents.append({"local_off": r[0], "data_off": r[1], "csize": r[2], "usize": r[3], "crc32": r[4], "method": r[5] & 0xFFFF,
+                     "gpflags": r[5] >> 16, "name_off": r[6], "name_len": r[7] & 0xFFFF, "ok": r[7] >> 16})
+    return ents
 
 
 # ---- generators -------------------------------------------------------------------------------------------------
