@@ -47,31 +47,37 @@ crc32_jobs_kernel(const CrcJob* __restrict__ jobs, uint32_t njobs, uint32_t* __r
   tab[threadIdx.x] = c_crc_table[threadIdx.x];
   __syncthreads();
   for (uint32_t j = blockIdx.x; j < njobs; j += gridDim.x) {
-    const CrcJob   job = jobs[j];
-    const uint32_t lo  = threadIdx.x * kCrcSlice;
-    const uint32_t n   = job.len > lo ? (job.len - lo < kCrcSlice ? job.len - lo : kCrcSlice) : 0u;
-    const uint8_t* p   = job.p + lo;
+    const CrcJob job = jobs[j];
+    // The job is taken as if it had leading zero bytes up to 64 KiB (they do not change a raw CRC): slice t then
+    // always ENDS 256 * (255 - t) bytes before the job's end, and the slices combine with fixed shifts.
+    const int64_t  s0 = (int64_t)job.len - (int64_t)kCrcJobBytes + (int64_t)threadIdx.x * kCrcSlice;   // may be < 0
+    const uint32_t lo = s0 < 0 ? 0u : (uint32_t)s0;
+    const int64_t  hi = s0 + kCrcSlice;
+    const uint32_t n  = hi > 0 ? (uint32_t)hi - lo : 0u;
+    const uint8_t* p  = job.p + lo;
     uint32_t crc = 0;
     uint32_t i = 0;
-    if ((((uintptr_t)p) & 15u) == 0u) {
-      for (; i + 16u <= n; i += 16u) {
-        const uint4 v = __ldg(reinterpret_cast<const uint4*>(p + i));
-        const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+    for (; i < n && (((uintptr_t)(p + i)) & 15u); i++) crc = tab[(crc ^ __ldg(p + i)) & 255u] ^ (crc >> 8);
+    for (; i + 16u <= n; i += 16u) {
+      const uint4 v = __ldg(reinterpret_cast<const uint4*>(p + i));
+      const uint32_t w[4] = {v.x, v.y, v.z, v.w};
 #pragma unroll
-        for (int k = 0; k < 4; k++) {
-          uint32_t x = w[k];
+      for (int k = 0; k < 4; k++) {
+        uint32_t x = w[k];
 #pragma unroll
-          for (int b = 0; b < 4; b++) { crc = tab[(crc ^ x) & 255u] ^ (crc >> 8); x >>= 8; }
-        }
+        for (int b = 0; b < 4; b++) { crc = tab[(crc ^ x) & 255u] ^ (crc >> 8); x >>= 8; }
       }
     }
     for (; i < n; i++) crc = tab[(crc ^ __ldg(p + i)) & 255u] ^ (crc >> 8);
-    // bring the slice to the end of the job: append the bytes that follow it
-    const uint32_t after = job.len > lo + n ? job.len - lo - n : 0u;
-    part[threadIdx.x] = n ? crc_shift(crc, after) : 0u;
+    part[threadIdx.x] = crc;
     __syncthreads();
-    for (uint32_t s = 128; s > 0; s >>= 1) {
-      if (threadIdx.x < s) part[threadIdx.x] ^= part[threadIdx.x + s];
+    // tree: raw(A || B) = shift(raw(A), |B|) ^ raw(B) with |B| = 256 * 2^k at level k (matrix 8 + k, one broadcast
+    // constant-memory read per row)
+#pragma unroll 1
+    for (uint32_t k = 0; k < 8; k++) {
+      const uint32_t step = 1u << k;
+      if ((threadIdx.x & (2u * step - 1u)) == 0u)
+        part[threadIdx.x] = crc_mat_apply(c_crc_shift[8 + k], part[threadIdx.x]) ^ part[threadIdx.x + step];
       __syncthreads();
     }
     if (threadIdx.x == 0) raw_out[j] = part[0];
