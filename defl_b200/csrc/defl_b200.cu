@@ -778,7 +778,8 @@ struct PipeSlot {
   size_t first = 0, count = 0;
 };
 
-constexpr int kPipeSlots = 3;    // chunk c+1 is on its way in while chunk c decodes and chunk c-1 is on its way out
+constexpr int kPipeSlots = 6;    // at most; DEFL_PIPE_SLOTS (default 3) are used: chunk c+1 is on its way in while chunk c
+                                 // decodes and chunk c-1 is on its way out
 struct HostPipe {
   PipeSlot slot[kPipeSlots];
   bool     ready = false;
@@ -786,8 +787,8 @@ struct HostPipe {
 HostPipe g_pipes[kMaxDevices];
 
 constexpr size_t kGapMerge   = 512;          // input runs this close in host memory are copied as one
-constexpr size_t kChunkMin   = 64u << 20;    // bytes (in + out) per chunk, at least
-constexpr size_t kChunkCount = 32;           // aim for this many chunks in a large batch (the first chunk's way in and the
+constexpr size_t kChunkMin   = 48u << 20;    // bytes (in + out) per chunk, at least
+constexpr size_t kChunkCount = 96;           // aim for this many chunks in a large batch (the first chunk's way in and the
                                              // last one's way out overlap with nothing: keep them small)
 
 int chunk_submit(Engine* E, PipeSlot& S, const infl_batch_item_t* items, size_t first, size_t count, int flags) {
@@ -931,7 +932,9 @@ int run_host_batch_on_device(const infl_batch_item_t* items, size_t n, int flags
       return rc2;
     }
   }
-  const size_t chunk_bytes = std::max(kChunkMin, total / kChunkCount + 1);
+  static const size_t chunk_count = env_u32("DEFL_CHUNK_COUNT", (uint32_t)kChunkCount, 1, 4096);
+  static const int    slots = (int)env_u32("DEFL_PIPE_SLOTS", 3, 1, kPipeSlots);
+  const size_t chunk_bytes = std::max(kChunkMin, total / chunk_count + 1);
 
   size_t first = 0;
   int    c = 0, rc = UNZ_OK;
@@ -941,13 +944,13 @@ int run_host_batch_on_device(const infl_batch_item_t* items, size_t n, int flags
       bytes += items[first + count].srclen + items[first + count].dstlen;
       count++;
     }
-    PipeSlot& S = HP.slot[c % kPipeSlots];
-    if (c >= kPipeSlots) rc = chunk_finish(S, items, results);      // the chunk that used this slot is home
+    PipeSlot& S = HP.slot[c % slots];
+    if (c >= slots) rc = chunk_finish(S, items, results);           // the chunk that used this slot is home
     if (rc == UNZ_OK) rc = chunk_submit(E, S, items, first, count, flags);
     first += count;
     c++;
   }
-  for (int k = std::max(0, c - kPipeSlots); k < c && rc == UNZ_OK; k++) rc = chunk_finish(HP.slot[k % kPipeSlots], items, results);
+  for (int k = std::max(0, c - slots); k < c && rc == UNZ_OK; k++) rc = chunk_finish(HP.slot[k % slots], items, results);
   for (PipeSlot& S : HP.slot) {
     const cudaError_t e = cudaStreamSynchronize(S.st);
     if (e != cudaSuccess && rc == UNZ_OK) rc = fail("D2H output", e);
