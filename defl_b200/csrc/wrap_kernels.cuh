@@ -268,6 +268,57 @@ png_unfilter_kernel(PngJob* __restrict__ jobs, uint32_t njobs) {
     const uint32_t bpp = job.bpp, stride = job.stride, npx = (stride + bpp - 1) / bpp;   // steps per row
     const size_t   rawstride = (size_t)stride + 1;
     bool bad = false;
+    if (bpp == 4u && (stride & 3u) == 0u && (((uintptr_t)job.pix) & 3u) == 0u) {
+      // 4-byte pixels (RGBA8, grey + alpha 16): a pixel is one 32-bit word.  The scanline data is read as aligned
+      // words two steps ahead of their use (the row starts 1 byte after the filter byte, so a pixel straddles two
+      // words: one funnel shift), the result is stored as one word; the four byte lanes are computed on packed bytes.
+      for (uint32_t y0 = 0; y0 < job.height; y0 += 32) {
+        const uint32_t y = y0 + lane;
+        const bool     live = y < job.height;
+        const uint8_t* src = job.raw + (size_t)(live ? y : 0) * rawstride;
+        uint32_t*      dst = reinterpret_cast<uint32_t*>(job.pix + (size_t)(live ? y : 0) * stride);
+        const uint32_t ft = live ? src[0] : 0u;
+        bad = bad || ft > 4u;
+        const uint32_t* up_row = (y0 > 0) ? reinterpret_cast<const uint32_t*>(job.pix + (size_t)(y0 - 1) * stride) : nullptr;
+        const uint32_t* sw = reinterpret_cast<const uint32_t*>((uintptr_t)(src + 1) & ~(uintptr_t)3);
+        const uint32_t  sh = (uint32_t)((uintptr_t)(src + 1) & 3u) * 8u;
+        const uint32_t  nwords = npx + 1;                      // aligned words that hold the row's bytes (one more when sh != 0)
+        uint32_t w0 = live ? __ldg(sw) : 0u, w1 = (live && 1u < nwords) ? __ldg(sw + 1) : 0u, w2 = 0u;
+        uint32_t A = 0, C = 0, CUR = 0;
+        for (uint32_t t = 0; t < npx + 31; t++) {
+          const uint32_t s = t - lane;
+          const bool act = live && t >= lane && s < npx;
+          if (act && s + 2u < nwords) w2 = __ldg(sw + s + 2u);  // lands while the next two pixels are computed
+          uint32_t UP = __shfl_up_sync(0xFFFFFFFFu, CUR, 1);
+          if (lane == 0) UP = (act && up_row) ? up_row[s] : 0u;
+          if (act) {
+            const uint32_t r = __funnelshift_r(w0, w1, sh);
+            uint32_t pred;
+            switch (ft) {
+              case 1:  pred = A; break;
+              case 2:  pred = UP; break;
+              case 3:  pred = (A & UP) + (((A ^ UP) & 0xFEFEFEFEu) >> 1); break;      // per-byte floor((a + b) / 2)
+              case 4: {
+                pred = 0;
+#pragma unroll
+                for (int k = 0; k < 4; k++)
+                  pred |= paeth((A >> (8 * k)) & 255u, (UP >> (8 * k)) & 255u, (C >> (8 * k)) & 255u) << (8 * k);
+                break;
+              }
+              default: pred = 0; break;
+            }
+            // per-byte add modulo 256
+            const uint32_t v = ((r & 0x7F7F7F7Fu) + (pred & 0x7F7F7F7Fu)) ^ ((r ^ pred) & 0x80808080u);
+            dst[s] = v;
+            A = v; C = UP; CUR = v;
+            w0 = w1; w1 = w2;
+          }
+        }
+        __syncwarp();
+      }
+      if (__any_sync(0xFFFFFFFFu, bad) && lane == 0) jobs[j].bad = 1;
+      continue;
+    }
     for (uint32_t y0 = 0; y0 < job.height; y0 += 32) {
       const uint32_t y = y0 + lane;
       const bool     live = y < job.height;
