@@ -6,6 +6,9 @@ import subprocess
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libdefl_b200.so")
+# the same sources with the retired engines compiled in (v1 group per stream, v2 lane-decoder pipeline): only the
+# cross-check tests load it (tests/conftest.py gpu_lib_legacy); the product library does not carry them
+LIB_LEGACY = os.path.join(HERE, "libdefl_b200_legacy.so")
 SOURCES = ["defl_b200.cu"]
 DEPS = sorted(f for f in os.listdir(CSRC) if f.endswith((".cu", ".cuh", ".inc"))) + \
        ["../../include/defl/infl.h", "../../include/defl/infl_batch.h", "../../include/defl/common.h", "../../include/defl/infl_wrap.h"]
@@ -25,10 +28,11 @@ def _nvcc():
     raise RuntimeError("nvcc not found: libdefl_b200.so cannot be built (there is no CPU fallback)")
 
 
-def stale():
-    if not os.path.exists(LIB):
+def stale(lib=None):
+    lib = lib or LIB
+    if not os.path.exists(lib):
         return True
-    t = os.path.getmtime(LIB)
+    t = os.path.getmtime(lib)
     for d in DEPS:
         p = os.path.join(CSRC, d)
         if os.path.exists(p) and os.path.getmtime(p) > t:
@@ -36,20 +40,23 @@ def stale():
     return False
 
 
-def build(force=False, verbose=False):
-    if not force and not stale():
-        return LIB
+def build(force=False, verbose=False, legacy=False):
+    lib = LIB_LEGACY if legacy else LIB
+    if not force and not stale(lib):
+        return lib
     extra = os.environ.get("DEFL_NVCC_EXTRA", "").split()          # experiments only (e.g. -DDEFL_WARP_CTAS_PER_SM=10)
+    if legacy:
+        extra.append("-DDEFL_LEGACY_ENGINES")
     cmd = [_nvcc()] + NVCC_FLAGS + extra + (["-Xptxas", "-v"] if verbose else []) + \
-          ["-o", LIB] + [os.path.join(CSRC, s) for s in SOURCES]
+          ["-o", lib] + [os.path.join(CSRC, s) for s in SOURCES]
     out = subprocess.run(cmd, capture_output=True, text=True)
     if out.returncode != 0:
         raise RuntimeError("nvcc failed:\n" + out.stdout + out.stderr)
     if verbose:
         print(out.stderr)
-    return LIB
+    return lib
 
 
 if __name__ == "__main__":
     import sys
-    print(build(force="--force" in sys.argv, verbose="-v" in sys.argv))
+    print(build(force="--force" in sys.argv, verbose="-v" in sys.argv, legacy="--legacy" in sys.argv))

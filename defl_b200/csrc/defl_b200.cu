@@ -35,6 +35,7 @@ using defl::GroupSmem;
 thread_local std::string      g_last_error;
 std::atomic<uint64_t>         g_launches{0};
 std::atomic<int>              g_lanes_per_stream{0};
+std::atomic<int>              g_pipeline_shape{0};
 
 
 int fail(const char* what, cudaError_t e = cudaSuccess) {
@@ -134,6 +135,7 @@ int engine_for_current_device(Engine** out) {
 }
 
 // ---- kernel launch ------------------------------------------------------------------------------------
+#ifdef DEFL_LEGACY_ENGINES   // v1 (group per stream) and v2 (lane-decoder pipeline): cross-check builds only (python -m defl_b200.build --legacy)
 template <int G, int GROUPS>
 int launch_batch(int sms, const infl_batch_item_t* d_items, const uint32_t* d_order, uint32_t n, int flags,
                  infl_batch_result_t* d_results, unsigned int* d_ticket, cudaStream_t st) {
@@ -161,7 +163,6 @@ int launch_batch(int sms, const infl_batch_item_t* d_items, const uint32_t* d_or
   return UNZ_OK;
 }
 
-std::atomic<int> g_pipeline_shape{0};
 
 template <int D, int SL, int K>
 int launch_pipeline(int sms, const infl_batch_item_t* d_items, const uint32_t* d_order, uint32_t n, int flags,
@@ -188,6 +189,8 @@ int launch_pipeline(int sms, const infl_batch_item_t* d_items, const uint32_t* d
   g_launches.fetch_add(1, std::memory_order_relaxed);
   return UNZ_OK;
 }
+
+#endif  // DEFL_LEGACY_ENGINES
 
 // ---- v3 (default engine): one warp per stream --------------------------------------------------------------
 constexpr int    kWarpsPerCta = 4;
@@ -276,6 +279,7 @@ int launch_batch_any(int sms, const infl_batch_item_t* d_items, const uint32_t* 
     return launch_warp4(sms, d_items, d_order, (uint32_t)n, flags, d_results, d_ws, st);
   if (!lanes && g_engine.load() == 3)
     return launch_warp(sms, d_items, d_order, (uint32_t)n, flags, d_results, d_ws, st);
+#ifdef DEFL_LEGACY_ENGINES
   if (!lanes) {   // the lane-decoder pipeline (v2)
     switch (g_pipeline_shape.load()) {
       case 0:  return launch_pipeline<2, 24, 14>(sms, d_items, d_order, (uint32_t)n, flags, d_results, t, st);
@@ -298,6 +302,10 @@ int launch_batch_any(int sms, const infl_batch_item_t* d_items, const uint32_t* 
     case 32: return launch_batch<32, 4>(sms, d_items, d_order, (uint32_t)n, flags, d_results, t, st);
     default: return fail("lanes per stream must be 1, 2, 4, 8, 16 or 32");
   }
+#else
+  (void)t;
+  return fail("this build has the warp-per-stream engines only (engines 3 and 4); build with -DDEFL_LEGACY_ENGINES for 1 and 2");
+#endif
 }
 
 // longest serial decode first.  The work of a stream is its tokens (about its compressed size) plus its
@@ -787,8 +795,8 @@ struct HostPipe {
 HostPipe g_pipes[kMaxDevices];
 
 constexpr size_t kGapMerge   = 512;          // input runs this close in host memory are copied as one
-constexpr size_t kChunkMin   = 48u << 20;    // bytes (in + out) per chunk, at least
-constexpr size_t kChunkCount = 96;           // aim for this many chunks in a large batch (the first chunk's way in and the
+constexpr size_t kChunkMin   = 64u << 20;    // bytes (in + out) per chunk, at least
+constexpr size_t kChunkCount = 32;           // aim for this many chunks in a large batch (the first chunk's way in and the
                                              // last one's way out overlap with nothing: keep them small)
 
 int chunk_submit(Engine* E, PipeSlot& S, const infl_batch_item_t* items, size_t first, size_t count, int flags) {
@@ -1153,6 +1161,9 @@ UNZ_EXPORT const char* infl_engine_info(void) {
 UNZ_EXPORT uint64_t infl_kernel_launch_count(void) { return g_launches.load(); }
 
 UNZ_EXPORT int infl_set_lanes_per_stream(int lanes) {
+#ifndef DEFL_LEGACY_ENGINES
+  if (lanes != 0) return fail("the group-per-stream engine is not in this build (-DDEFL_LEGACY_ENGINES)");
+#endif
   if (lanes != 0 && lanes != 1 && lanes != 2 && lanes != 4 && lanes != 8 && lanes != 16 && lanes != 32)
     return fail("lanes per stream must be 0 (default), 1, 2, 4, 8, 16 or 32");
   g_lanes_per_stream.store(lanes);
@@ -1173,6 +1184,9 @@ UNZ_EXPORT size_t infl_batch_workspace_size(size_t n) {
 }
 
 UNZ_EXPORT int infl_set_engine(int engine) {
+#ifndef DEFL_LEGACY_ENGINES
+  if (engine == 1 || engine == 2) return fail("engines 1 and 2 are not in this build (-DDEFL_LEGACY_ENGINES)");
+#endif
   if (engine < 1 || engine > 4) return fail("engine must be 1 (group per stream), 2 (lane-decoder pipeline), 3 (warp per stream, v3) or 4 (v4)");
   g_engine.store(engine);
   return UNZ_OK;

@@ -2,7 +2,9 @@
 #pragma once
 #include "simt_cuda.cuh"
 #include "inflate_core.cuh"
+#ifdef DEFL_LEGACY_ENGINES
 #include "pipeline.cuh"
+#endif
 #include "warp_decode.cuh"
 #include "warp_decode4.cuh"
 #include "split_decode.cuh"
@@ -10,6 +12,7 @@
 
 namespace defl {
 
+#ifdef DEFL_LEGACY_ENGINES
 // K3: batch inflate.  Persistent CTAs; every group of G lanes pulls the next stream from a
 // global ticket counter (streams are pre-ordered largest-first by the host so the tail is
 // short), decodes it start to finish and writes one 32-byte result record.
@@ -88,6 +91,8 @@ inflate_pipeline_kernel(const infl_batch_item_t* __restrict__ items, const uint3
 
 template <int D, int SL, int K>
 constexpr size_t pipeline_smem_bytes() { return sizeof(Slot) * D * SL + sizeof(WorkerSmem) * K + 16; }
+
+#endif  // DEFL_LEGACY_ENGINES
 
 // K3 (v3, default): one warp per stream, the 32 lanes decode 32 sub-sequences of the current block at
 // once (warp_decode.cuh).  Persistent CTAs of WARPS warps; each warp owns a slice of the global token

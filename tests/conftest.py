@@ -47,3 +47,21 @@ def gpu_lib():
     torch.cuda.init()
     torch.zeros(1, device="cuda")
     return defl_b200
+
+
+@pytest.fixture(scope="session")
+def gpu_lib_legacy(gpu_lib):
+    """The same sources built with -DDEFL_LEGACY_ENGINES (defl_b200/libdefl_b200_legacy.so): the retired engines
+    v1 (group per stream) and v2 (lane-decoder pipeline) as cross-checks.  A second, independent instance of the
+    ctypes mirror bound to that library."""
+    import importlib.util
+    from defl_b200 import build as b
+    if not os.path.exists(b.LIB_LEGACY):
+        pytest.skip("libdefl_b200_legacy.so not built (python -m defl_b200.build --legacy)")
+    root = os.path.dirname(HERE)
+    spec = importlib.util.spec_from_file_location("defl_b200_legacy_api", os.path.join(root, "defl_b200", "api.py"))
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    mod.LIB_PATH = b.LIB_LEGACY
+    mod.lib()
+    return mod

@@ -30,9 +30,18 @@ def _check_against_port(d, res, outs, datas, caps, flags, what):
                 assert int(g["adler_stored"]) == r.adler_stored
 
 
-def test_corpus_raw_every_group_width(gpu_lib, corpus):
-    """the reference's own corpus (raw deflate, flags 0), test_files.c:174-257."""
+def test_corpus_raw_every_group_width(gpu_lib, gpu_lib_legacy, corpus):
+    """the reference's own corpus (raw deflate, flags 0), test_files.c:174-257: the default engine
+    of the product library, then every group width of the retired v1 engine (legacy build) as a cross-check."""
     d = gpu_lib
+    res, outs = d.infl_buf_batch([e["data"] for e in corpus], [e["cap"] for e in corpus], 0)
+    for e, g, out in zip(corpus, res, outs):
+        assert int(g["code"]) == e["ref_code"], e["name"]
+        if e["ref_code"] == 0:
+            assert hashlib.sha256(bytes(out)).hexdigest() == e["ref_sha256"], e["name"]
+    with pytest.raises(ValueError):
+        d.set_lanes_per_stream(8)                       # not in the product build
+    d = gpu_lib_legacy
     datas = [e["data"] for e in corpus]
     caps = [e["cap"] for e in corpus]
     try:
@@ -101,22 +110,23 @@ def test_reference_fuzzer_verdicts(gpu_lib, fuzz_ref):
             assert int(res[i]["code"]) == -1, i
 
 
-def test_mutants_vs_oracle(gpu_lib):
-    """Valid, truncated, bit-flipped, over-long streams; short / exact / oversized dst; zlib and raw."""
+def test_mutants_vs_oracle(gpu_lib, gpu_lib_legacy):
+    """Valid, truncated, bit-flipped, over-long streams; short / exact / oversized dst; zlib and raw.  Lanes 0 = the
+    product library's default engine; 1, 8, 32 = the retired group-per-stream engine of the legacy build."""
     from test_oracle import _mutants
-    d = gpu_lib
     by_flag = {0: ([], []), 1: ([], [])}
     for data, cap, flags, raw, m in _mutants(777, 2400):
         by_flag[flags][0].append(data)
         by_flag[flags][1].append(cap)
     try:
         for lanes in (0, 1, 8, 32):
+            d = gpu_lib if lanes == 0 else gpu_lib_legacy
             d.set_lanes_per_stream(lanes)
             for flags, (datas, caps) in by_flag.items():
                 res, outs = d.infl_buf_batch(datas, caps, flags)
                 _check_against_port(d, res, outs, datas, caps, flags, ("mutants", lanes, flags))
     finally:
-        d.set_lanes_per_stream(0)
+        gpu_lib_legacy.set_lanes_per_stream(0)
 
 
 def test_chunk_lists(gpu_lib, corpus):
@@ -223,7 +233,7 @@ def test_infl_stream_shim(gpu_lib, corpus):
     st.destroy()
 
 
-def test_edge_shapes(gpu_lib):
+def test_edge_shapes(gpu_lib, gpu_lib_legacy):
     """Longest match, farthest distance, overlapping short periods, empty/ragged batch members."""
     d = gpu_lib
     rnd = np.random.default_rng(5)
@@ -245,13 +255,14 @@ def test_edge_shapes(gpu_lib):
             caps.append(len(raw))
     try:
         for lanes in LANES:
-            d.set_lanes_per_stream(lanes)
-            res, outs = d.infl_buf_batch(datas, caps, d.INFL_ZLIB)
-            _check_against_port(d, res, outs, datas, caps, 1, ("edges", lanes))
+            dd = gpu_lib if lanes == 0 else gpu_lib_legacy
+            dd.set_lanes_per_stream(lanes)
+            res, outs = dd.infl_buf_batch(datas, caps, dd.INFL_ZLIB)
+            _check_against_port(dd, res, outs, datas, caps, 1, ("edges", lanes))
             for i, out in enumerate(outs):
                 assert bytes(out) == raws[i // 6]
     finally:
-        d.set_lanes_per_stream(0)
+        gpu_lib_legacy.set_lanes_per_stream(0)
     # an empty batch and NULL-sized members
     res, outs = d.infl_buf_batch([b"", zlib.compress(b"xyz")], [4, 3], d.INFL_ZLIB)
     assert int(res[0]["code"]) == 0 and int(res[0]["outlen"]) == 0 and bytes(outs[1]) == b"xyz"
@@ -307,10 +318,11 @@ def test_gather_kernel(gpu_lib):
     assert np.array_equal(out.cpu().numpy()[:total], want)
 
 
-def test_pipeline_shapes(gpu_lib):
-    """Every compiled (decoder warps, slots, worker warps) variant of the default engine, mixed payloads."""
+def test_pipeline_shapes(gpu_lib_legacy):
+    """Every compiled (decoder warps, slots, worker warps) variant of the retired lane-decoder pipeline (v2, legacy
+    build), mixed payloads."""
     from defl_b200 import synth
-    d = gpu_lib
+    d = gpu_lib_legacy
     specs = []
     for i in range(160):
         kind = ("text", "log", "png", "rand", "zero")[i % 5]
