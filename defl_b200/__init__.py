@@ -10,6 +10,7 @@ every decode call needs a CUDA device and raises/returns UNZ_ERR otherwise.
 from .api import (  # noqa: F401
     UNZ_OK, UNZ_ERR, UNZ_NOOP, UNZ_UNFINISHED, UNZ_EFULL, INFL_ZLIB,
     INFL_BATCH_VERIFY_ADLER, INFL_BATCH_DEVICE_PTRS, INFL_BATCH_ALL_GPUS, INFL_BATCH_NO_SPLIT,
+    INFL_BATCH_STATIC_MAX_STREAMS,
     ITEM_DTYPE, RESULT_DTYPE,
     lib, infl_buf, infl_buf_batch, infl_buf_batch_iov, InflStream, DeviceBatch, batch_partition,
     last_error, engine_info, kernel_launch_count, set_lanes_per_stream, set_pipeline_shape, set_engine,

@@ -20,6 +20,7 @@ INFL_BATCH_VERIFY_ADLER = 0x0100
 INFL_BATCH_DEVICE_PTRS = 0x0200
 INFL_BATCH_ALL_GPUS = 0x0400
 INFL_BATCH_NO_SPLIT = 0x0800
+INFL_BATCH_STATIC_MAX_STREAMS = 65536
 
 INFO_HAS_TRAILER = 1
 INFO_ADLER_MATCH = 2
@@ -36,7 +37,7 @@ EXPORTED_SYMBOLS = [
     "infl_init", "infl_reset", "infl_resize_output", "infl_include", "infl", "infl_reset_pool",
     "infl_destroy", "infl_buf", "infl_stream", "infl_output_pos", "infl_input_pos", "infl_adler32",
     "infl_buf_batch", "infl_buf_batch_iov", "infl_batch_workspace_size", "infl_batch_decode_device",
-    "infl_gather_device",
+    "infl_batch_decode_device_static", "infl_gather_device",
     "infl_batch_partition",
     "infl_device_count", "infl_last_error", "infl_engine_info",
     "infl_kernel_launch_count", "infl_set_lanes_per_stream", "infl_set_pipeline_shape", "infl_set_engine",
@@ -89,6 +90,8 @@ def lib():
     L.infl_batch_workspace_size.argtypes = [sz]
     L.infl_batch_decode_device.restype = i32
     L.infl_batch_decode_device.argtypes = [vp, vp, sz, i32, vp, vp, vp]
+    L.infl_batch_decode_device_static.restype = i32
+    L.infl_batch_decode_device_static.argtypes = [vp, vp, sz, i32, vp, vp]
     L.infl_batch_partition.restype = i32
     L.infl_batch_partition.argtypes = [vp, sz, i32, vp, vp]
     L.infl_gather_device.restype = i32

@@ -1203,6 +1203,63 @@ UNZ_EXPORT int infl_batch_decode_device(const infl_batch_item_t* d_items, const 
                           static_cast<cudaStream_t>(cuda_stream));
 }
 
+// ---- infl_batch_decode_device_static: the batch kernel with NO allocation anywhere on the call path ----------
+// The token scratch of the one-warp-per-stream kernel lives in a file-scope device array instead of a caller's
+// workspace: kStaticWarps warps' worth (37 CTAs x 4 warps = one warp per SM of a B200), about 37.6 MiB that every
+// GPU which loads this library holds until the process exits.  In HOST code `g_static_ws` is only a stand-in for
+// the symbol, not a device address: the address comes from cudaGetSymbolAddress, once per device, with that
+// device current, and that pointer is what the kernel gets.
+constexpr int      kStaticCtas       = 37;
+constexpr int      kStaticWarps      = kStaticCtas * kWarpsPerCta;                    // 148
+constexpr size_t   kStaticWsBytes    = kWsHeader + (size_t)kStaticWarps * defl::kWarpScratchBytes;
+constexpr size_t   kStaticMaxStreams = INFL_BATCH_STATIC_MAX_STREAMS;
+static __device__ __align__(256) unsigned char g_static_ws[kStaticWsBytes];
+
+struct StaticWs {
+  std::atomic<unsigned char*> ptr{nullptr};      // device address of g_static_ws on this device
+};
+static StaticWs   g_static[kMaxDevices];
+static std::mutex g_static_mu;
+
+UNZ_EXPORT int infl_batch_decode_device_static(const infl_batch_item_t* d_items, const uint32_t* d_order, size_t n,
+                                               int flags, infl_batch_result_t* d_results, void* cuda_stream) {
+  if (n == 0) return UNZ_OK;
+  if (!d_items || !d_results) return fail("infl_batch_decode_device_static: null device pointer");
+  if (n > kStaticMaxStreams)
+    return fail("infl_batch_decode_device_static: more than INFL_BATCH_STATIC_MAX_STREAMS (65536) streams in one call; "
+                "use infl_batch_decode_device with a workspace");
+  int dev = 0;
+  CU_TRY(cudaGetDevice(&dev), "cudaGetDevice (is a CUDA device visible? this library has no CPU path)");
+  if (dev < 0 || dev >= kMaxDevices) return fail("device index out of range");
+  unsigned char* ws = g_static[dev].ptr.load(std::memory_order_acquire);
+  if (!ws) {                                       // set-up, once per device, with that device current
+    std::lock_guard<std::mutex> g(g_static_mu);
+    ws = g_static[dev].ptr.load(std::memory_order_relaxed);
+    if (!ws) {
+      int major = 0;
+      CU_TRY(cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev), "cudaDeviceGetAttribute");
+      if (major < 10) return fail("this build contains sm_100a code only (needs a B200-class GPU)");
+      void* p = nullptr;
+      CU_TRY(cudaGetSymbolAddress(&p, g_static_ws), "cudaGetSymbolAddress(g_static_ws)");
+      if (!p) return fail("cudaGetSymbolAddress(g_static_ws) gave a null address");
+      CU_TRY(cudaFuncSetAttribute(defl::inflate_warp_kernel<kWarpsPerCta>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  (int)(sizeof(defl::WarpSmem) * kWarpsPerCta)), "cudaFuncSetAttribute(smem)");
+      ws = static_cast<unsigned char*>(p);
+      g_static[dev].ptr.store(ws, std::memory_order_release);
+    }
+  }
+  cudaStream_t st = static_cast<cudaStream_t>(cuda_stream);
+  const unsigned grid = (unsigned)std::min<uint64_t>((uint64_t)kStaticCtas, (n + kWarpsPerCta - 1) / kWarpsPerCta);
+  auto* ticket = reinterpret_cast<unsigned int*>(ws);
+  // the array keeps the last call's contents: the ticket counter must start at zero (token scratch need not)
+  CU_TRY(cudaMemsetAsync(ticket, 0, sizeof(unsigned int), st), "cudaMemsetAsync(ticket)");
+  defl::inflate_warp_kernel<kWarpsPerCta><<<grid, kWarpsPerCta * 32, sizeof(defl::WarpSmem) * kWarpsPerCta, st>>>(
+      d_items, d_order, (uint32_t)n, flags, d_results, ticket, ws + kWsHeader);
+  CU_TRY(cudaGetLastError(), "inflate_warp_kernel launch (static scratch)");
+  g_launches.fetch_add(1, std::memory_order_relaxed);
+  return UNZ_OK;
+}
+
 UNZ_EXPORT int infl_gather_device(const void* const* d_seg_src, const uint64_t* d_seg_len,
                                   const uint64_t* d_seg_dst_off, size_t nseg, void* d_out, void* cuda_stream) {
   if (nseg == 0) return UNZ_OK;

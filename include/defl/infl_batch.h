@@ -90,6 +90,22 @@ UNZ_EXPORT int infl_batch_decode_device(const infl_batch_item_t *d_items, const 
                                         size_t n, int flags, infl_batch_result_t *d_results,
                                         void *d_workspace, void *cuda_stream);
 
+/* The same decode with NO allocation on the call path.  This entry point has no counterpart in the
+   reference; it was added for callers that cannot call
+   cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  The
+   kernel's token scratch is a file-scope `static __device__` array inside the library (about
+   37.6 MiB: 148 warps' worth, held by every GPU that loads the library until the process exits), so
+   no workspace is passed and neither cudaMalloc / cudaFree nor any allocating library routine is
+   called.  Limits: n <= INFL_BATCH_STATIC_MAX_STREAMS per call (more => UNZ_ERR and a message in
+   infl_last_error(); use infl_batch_decode_device), 148 warps work at a time however large the GPU,
+   always the default (v3) engine.  Every call on a device shares the one array: calls that overlap
+   on the GPU (two streams, two threads) race on it -- order them on one stream or with events.
+   d_items, d_results, d_order as for infl_batch_decode_device; asynchronous on `cuda_stream`. */
+#define INFL_BATCH_STATIC_MAX_STREAMS 65536
+UNZ_EXPORT int infl_batch_decode_device_static(const infl_batch_item_t *d_items, const uint32_t *d_order,
+                                               size_t n, int flags, infl_batch_result_t *d_results,
+                                               void *cuda_stream);
+
 /* Gather pieces into contiguous device memory: for i < nseg copies
    seg_src[i][0..seg_len[i]) to d_out + seg_dst_off[i].  All arrays are device arrays. */
 UNZ_EXPORT int infl_gather_device(const void *const *d_seg_src, const uint64_t *d_seg_len,
