@@ -6,7 +6,8 @@ import os
 import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libdefl_b200.so")
+# DEFL_B200_LIB: another build of the same library (A/B experiments, profiles/tools); the default is the in-tree one
+LIB_PATH = os.environ.get("DEFL_B200_LIB") or os.path.join(HERE, "libdefl_b200.so")
 
 # UnzResult, reference include/defl/common.h:80-90
 UNZ_UNFINISHED = 2

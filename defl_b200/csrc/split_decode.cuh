@@ -227,7 +227,7 @@ DEFL_DEV uint64_t fixed_probe_lane(const uint16_t* lit, const uint16_t* dist, co
     if (r >= target) return r;
     uint32_t tok, used;
     const uint64_t left = end_bit - r;
-    const uint32_t s = decode_token(lit, dist, br, left > 0x7FFFFFFFull ? 0x7FFFFFFFu : (uint32_t)left, false, tok, used);
+    const uint32_t s = decode_token(lit, dist, br, left > 0x7FFFFFFFull ? 0x7FFFFFFFu : (uint32_t)left, 0u, tok, used);
     if (s == LS_OK) { r += used; br.consume(used); continue; }
     // Not yet on the true trajectory, the bits may spell a code that does not exist or an end-of-block that is
     // none: step one bit and go on, the trajectory is still to be met.  (A true end of block that is followed by

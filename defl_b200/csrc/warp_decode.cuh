@@ -27,10 +27,11 @@ namespace defl {
 
 constexpr uint32_t kSubMax    = 8192;                 // bits per lane per window, at most
 constexpr uint32_t kSubMin    = 512;
-constexpr uint32_t kCpBits    = 128;                  // checkpoint spacing
-constexpr uint32_t kCpPerLane = kSubMax / kCpBits;
-constexpr uint32_t kSpecCap   = 1024;                 // tokens per lane per window (speculative pass)
+constexpr uint32_t kSubGrain  = 128;                  // a sub-sequence is a multiple of this many bits
+constexpr uint32_t kCpTokens  = 8;                    // checkpoint spacing: where every 8th speculative token starts
+constexpr uint32_t kSpecCap   = 1024;                 // tokens per lane per window (speculative pass, warm-up included)
 constexpr uint32_t kFixCap    = 1024;                 // tokens per lane per window (fix-up pass)
+constexpr uint32_t kCpPerLane = kSpecCap / kCpTokens;
 constexpr size_t   kWarpScratchBytes = 32u * (kSpecCap + kFixCap) * 4u + 32u * kCpPerLane * 2u;
 static_assert(kWarpScratchBytes % 16 == 0, "scratch slices stay 16-byte aligned");
 
@@ -100,52 +101,62 @@ struct SubReader {
 // time into a register: a quarter of the load instructions and of the L2 sectors touched (the lanes of an SM stream
 // through more lines than its L1 holds, so a 4-byte load mostly paid for a whole sector), and nothing waits for a
 // quad until four to eight words after it was requested.  drain() before the shared memory is used for anything else.
+// Words are counted from the 16-byte boundary at or below the stream's first word, so a refill is a shift, a mask and
+// one LDS; what lies past the stream's last word is zero-filled by the copy itself (its source size ends there).
 struct RingReader {
-  const uint32_t* w;
-  uint32_t        wend, widx;
   uint32_t        w0, w1, w2;
   uint32_t        bo;
+  uint32_t        ai;              // the word that enters the window next (16-byte-boundary numbering)
+  uint32_t        aend;            // one past the stream's last word, same numbering
   uint32_t*       ring;            // this lane's 4 words of slot 0
-  uint32_t        skew;            // words between w and the 16-byte boundary below it (0..3)
   const uint8_t*  quads;           // that boundary
 
-  // quad q holds words 4q - skew .. 4q - skew + 3 of the stream
+  // quad q holds words 4q .. 4q + 3
   DEFL_DEV void request(uint32_t q) {
-    const bool in = 4u * q < wend + skew;               // its first word may lie before w: same 16 bytes, never read
-    simt::cp_async16(ring + (q & 1u) * 128u, quads + (in ? (size_t)q * 16u : 0u), in);
+    const uint32_t first = 4u * q;
+    const uint32_t nw = first < aend ? (aend - first < 4u ? aend - first : 4u) : 0u;
+    simt::cp_async16_n(ring + (q & 1u) * 128u, quads + (nw ? (size_t)q * 16u : 0u), nw * 4u);
     simt::cp_async_commit();
   }
-  DEFL_DEV void from(const SubReader& s, uint32_t* ring_lane) {
-    w = s.w; wend = s.wend; widx = s.widx; w0 = s.w0; w1 = s.w1; w2 = s.w2; bo = s.bo; ring = ring_lane;
-    skew  = (uint32_t)(((uintptr_t)w >> 2) & 3u);
+  DEFL_DEV void seek(const uint32_t* w, uint32_t wend, uint32_t word, uint32_t bit, uint32_t* ring_lane) {
+    const uint32_t widx = word + (bit >> 5);
+    const uint32_t skew = (uint32_t)(((uintptr_t)w >> 2) & 3u);
+    bo = bit & 31u;
+    w0 = widx < wend ? simt::ld_in32(w + widx) : 0u;
+    w1 = widx + 1u < wend ? simt::ld_in32(w + widx + 1u) : 0u;
+    w2 = widx + 2u < wend ? simt::ld_in32(w + widx + 2u) : 0u;
+    ring  = ring_lane;
     quads = reinterpret_cast<const uint8_t*>((uintptr_t)w & ~(uintptr_t)15);
-    const uint32_t q = (widx + 3u + skew) >> 2;          // the quad of the next word the window needs
-    request(q); request(q + 1u);
+    aend  = wend + skew;
+    ai    = widx + 3u + skew;
+    request(ai >> 2); request((ai >> 2) + 1u);
   }
   DEFL_DEV void consume(uint32_t n) {     // n <= 48, bo < 32 on entry
     bo += n;
+    // a loop, not two ifs: if-converted, the second step's moves wait for the word the first step has only just
+    // asked for, taken or not
 #pragma unroll 1
     while (bo >= 32u) {
-      const uint32_t i = widx + 3u;                      // the word that enters the window
-      const uint32_t a = i + skew, q = a >> 2, k = a & 3u;
-      simt::cp_async_wait<1>();                          // quad q has landed (q + 1 may still be on its way)
-      const uint32_t v = ring[(q & 1u) * 128u + k];
-      w0 = w1; w1 = w2; w2 = i < wend ? v : 0u;
-      if (k == 3u) request(q + 2u);                      // its slot is free now
-      widx++; bo -= 32u;
+      simt::cp_async_wait<1>();                          // the quad of word ai has landed (the next may be on its way)
+      w0 = w1; w1 = w2;
+      w2 = ring[(ai & 4u) * 32u + (ai & 3u)];
+      if ((ai & 3u) == 3u) request((ai >> 2) + 2u);      // its slot is free now
+      ai++; bo -= 32u;
     }
   }
   DEFL_DEV void drain() { simt::cp_async_wait<0>(); }
 };
 
 DEFL_DEV uint32_t fail_stat(uint32_t reason) { return LS_FAIL | (reason << 8); }
+DEFL_DEV uint32_t low_bits(uint32_t v, uint32_t n) { return v & ~(0xFFFFFFFFu << n); }    // n < 32
 
 // Decode the token that starts at the reader's position.  `avail` = input bits from here to the end
 // of the stream; a symbol whose bits are not all there fails (infl.c:741-745,806-810).
+// A second literal joins the first in one token when it starts less than `pack_before` bits from here (0: never).
 // Returns LS_OK with (tok, used), LS_EOB with used = the code's bits, or LS_FAIL | reason << 8.
 template <typename READER>
 DEFL_DEV uint32_t decode_token(const uint16_t* lit, const uint16_t* dist, const READER& br, uint32_t avail,
-                               bool pack, uint32_t& tok, uint32_t& used) {
+                               uint32_t pack_before, uint32_t& tok, uint32_t& used) {
   const uint32_t v0 = simt::funnel_r(br.w0, br.w1, br.bo);
   const uint32_t v1 = simt::funnel_r(br.w1, br.w2, br.bo);
   uint32_t       e  = lit[v0 & (kLitRoot - 1)];
@@ -175,7 +186,7 @@ DEFL_DEV uint32_t decode_token(const uint16_t* lit, const uint16_t* dist, const 
   } else {
     const uint32_t x   = lit[v2 & (kLitRoot - 1)];
     const uint32_t xcl = (x >> 11) & 15u;
-    const bool two = pack && (x & (kLitIsLen | kLitKind)) == 0u && x != 0u && use1 + xcl <= avail;
+    const bool two = use1 < pack_before && (x & (kLitIsLen | kLitKind)) == 0u && x != 0u && use1 + xcl <= avail;
     use2 = two ? xcl : 0u;
     tok  = two ? ((2u << 24) | ((x & 255u) << 8) | val) : ((1u << 24) | val);
   }
@@ -188,139 +199,129 @@ DEFL_DEV uint32_t decode_token(const uint16_t* lit, const uint16_t* dist, const 
 struct LaneTraj {
   uint32_t land;   // window-relative bit where its trajectory ended (first token start >= its limit, or the stop)
   uint32_t stat;   // LS_*
-  uint32_t n;      // speculative tokens written
+  uint32_t n;      // speculative tokens written (warm-up tokens in front included)
   uint32_t m;      // first speculative token that belongs to the true trajectory
   uint32_t nf;     // fix-up tokens in front of them
   uint32_t T;      // where its true trajectory starts
-  uint32_t ncp;    // checkpoints its speculative pass recorded
+  uint32_t org;    // checkpoint c says: speculative token kCpTokens * c starts at bit org + cps[c]
+  uint32_t ncp;    // checkpoints recorded (the v4 engine's own scheme, warp_decode4.cuh)
   uint32_t s_land, s_stat, s_n;   // how the speculative trajectory ended (valid again after any later merge)
 };
 
 // speculative pass: decode from `start` (window-relative bits) to `limit`.
-// The inner loop is the hot loop of the whole engine, so it is written for the instruction count: no
-// end-of-input arithmetic (it stops 64 bits short of the end; decode_token() takes over there, and for
-// anything unusual -- end of block, a pattern no code maps to), one code path for "length + distance" and
-// "literal + maybe a second literal" (the second lookup goes to lit[] or dist[] by index, not by branch),
-// running pointers for the token and checkpoint stores.
+// The loop is the hot loop of the whole engine, so it is written for the instruction count:
+//  * every trip yields exactly one token, so the lanes' token counts move in step and the checkpoint store (where
+//    every 8th token starts) is a uniform branch, taken by all lanes in the same trip;
+//  * the warm-up runs in the same loop: the lane starts `warm` bits early and simply remembers which token was the
+//    first to start at or after `start` (tj.m; the tokens before it stay in the segment, unused).  Codes
+//    self-synchronise, so by then the lane is most likely ON the true trajectory and its first kept token starts
+//    exactly where its predecessor will end: no fix-up needed.  If the warm-up runs into anything that is not a
+//    token (end of block, no code) the lane starts again, blind, at `start`;
+//  * a second literal joins a token only if it STARTS before the end of the phase (start for the warm-up, limit
+//    after it), so that a trajectory leaves a phase on the first SYMBOL boundary at or after its end -- the same
+//    one for a lane and for its warmed-up successor, however their literal pairs fell;
+//  * no end-of-input arithmetic (it stops 64 bits short of the end; decode_token() takes over there, and for
+//    anything unusual), one code path for "length + distance" and "literal + maybe a second literal" (the second
+//    lookup goes to lit[] or dist[] by index, not by branch), a 32-bit token index.
 DEFL_DEV void lane_spec(const uint16_t* lit, const uint16_t* dist, const uint32_t* words, uint32_t wend,
                         uint32_t bw, uint32_t start, uint32_t limit, uint32_t endr, uint32_t* seg,
-                        uint16_t* cps, LaneTraj& tj, uint32_t warm, uint32_t* ring_lane,
-                        uint32_t* stop_lane = nullptr, uint32_t lane = 0) {
-  SubReader br;
-  br.w = words; br.wend = wend;
-  uint32_t r = start;
-  if (warm) {
-    // Warm-up: start `warm` bits early and throw the tokens away.  Codes self-synchronise, so by the time the
-    // lane reaches its sub-sequence it is most likely ON the true trajectory and its first kept token starts
-    // exactly where its predecessor will end: no fix-up needed.  If the warm-up runs into anything that is not
-    // a token (end of block, no code) the lane starts blind at `start`, as it would have without it.
-    uint32_t q = start - warm;
-    br.seek(bw, q);
-    bool ok = true;
-#pragma unroll 1
-    while (q < start) {
-      uint32_t tok, used;
-      if (decode_token(lit, dist, br, endr > q ? endr - q : 0u, false, tok, used) != LS_OK) { ok = false; break; }
-      q += used;
-      br.consume(used);
-    }
-    if (ok) r = q; else br.seek(bw, start);
-  } else {
-    br.seek(bw, start);
-  }
-  const uint32_t  r0 = r;
+                        uint16_t* cps, LaneTraj& tj, uint32_t warm, uint32_t* ring_lane) {
   RingReader rr;
-  rr.from(br, ring_lane);
-  uint32_t        next_cp = start, stat = LS_OK;
-  uint32_t*       tp = seg;
-  uint32_t* const tend = seg + kSpecCap;
-  uint16_t*       cpp = cps;
-  const uint32_t  fast_limit = endr >= 64u ? (limit < endr - 64u ? limit : endr - 64u) : 0u;
-  const uint32_t  dist_at = (uint32_t)(dist - lit);          // dist[] follows lit[] in shared memory
+  uint32_t   org = start - warm;
+  uint32_t   r = org, r0 = start, m0 = 0, ti = 0, stat = LS_OK;
+  uint32_t   lim = warm ? start : limit;                       // the end of the current phase
+  bool       warming = warm != 0u;
+  rr.seek(words, wend, bw, r, ring_lane);
+  const uint32_t  endr64  = endr >= 64u ? endr - 64u : 0u;
+  const uint32_t  dist_at = (uint32_t)(dist - lit);            // dist[] follows lit[] in shared memory
   for (;;) {
-    // ---- fast loop
-    while (r < fast_limit && tp != tend) {
-      const uint32_t v0 = simt::funnel_r(rr.w0, rr.w1, rr.bo);
-      const uint32_t v1 = simt::funnel_r(rr.w1, rr.w2, rr.bo);
-      uint32_t       e  = lit[v0 & (kLitRoot - 1)];
-      if ((e & (kLitIsLen | kLitKind)) == kLitSub)
-        e = lit[kLitRoot + (e & 0x1FFu) + ((v0 >> kLitRootBits) & ((1u << ((e >> 11) & 15u)) - 1u))];
-      if (e < 0x0800u || (e & (kLitIsLen | kLitKind)) == kLitEob) break;   // no code here / end of block
-      const bool     is_len = (e & kLitIsLen) != 0u;
-      const uint32_t cl   = (e >> 11) & 15u;
-      const uint32_t xb   = (e >> 8) & 7u;                        // 0 for a literal
-      const uint32_t val  = (e & 255u) + simt::bfe(v0, cl, xb);   // byte, or length - 3
-      const uint32_t use1 = cl + xb;
-      const uint32_t v2   = simt::funnel_r(v0, v1, use1);         // the 32 bits after this symbol
-      uint32_t       x    = lit[is_len ? dist_at + (v2 & (kDistRoot - 1)) : (v2 & (kLitRoot - 1))];
-      if (is_len && (x & kDistSub))
-        x = dist[kDistRoot + (x & 0x1FFu) + ((v2 >> kDistRootBits) & ((1u << ((x >> 11) & 15u)) - 1u))];
-      if (is_len && x == 0u) break;                               // no distance code here
-      const uint32_t xcl = (x >> 11) & 15u;
-      const uint32_t dxb = (x >> 7) & 15u;
-      const uint32_t d1  = ((x & 3u) << dxb) + simt::bfe(v2, xcl, dxb);          // distance - 1
-      const bool     two = (x & (kLitIsLen | kLitKind)) == 0u && x >= 0x0800u;   // a second literal follows
-      const uint32_t tok = is_len ? (kTokIsMatch | (d1 << 9) | (val + 3u))
-                                  : (two ? ((2u << 24) | ((x & 255u) << 8) | val) : ((1u << 24) | val));
-      const uint32_t used = use1 + (is_len ? xcl + dxb : (two ? xcl : 0u));
-      if (r >= next_cp) {
-        *cpp++ = (uint16_t)((r - next_cp) | ((uint32_t)(tp - seg) << 6));
-        next_cp += kCpBits;
-        // a lane below met the end of the block: most likely nothing from here on belongs to it.  Stop as if the
-        // token segment was full (if that lane was off the true trajectory, the next window starts here).
-        if (stop_lane && lane > *reinterpret_cast<volatile uint32_t*>(stop_lane)) { stat = LS_FULL; break; }
-      }
-      *tp++ = tok;
+    const uint32_t fast_limit = lim < endr64 ? lim : endr64;
+    // ---- fast loop: a checkpoint, then up to kCpTokens tokens
+    while (r < fast_limit && ti < kSpecCap) {
+      if ((ti & (kCpTokens - 1u)) == 0u) cps[ti / kCpTokens] = (uint16_t)(r - org);
+      bool odd = false;                                           // something that is not a token
+#pragma unroll 1
+      do {
+        const uint32_t v0 = simt::funnel_r(rr.w0, rr.w1, rr.bo);
+        uint32_t       e  = lit[v0 & (kLitRoot - 1)];
+        if ((e & (kLitIsLen | kLitKind)) == kLitSub)
+          e = lit[kLitRoot + (e & 0x1FFu) + low_bits(v0 >> kLitRootBits, (e >> 11) & 15u)];
+        if (e < 0x0800u || (e & (kLitIsLen | kLitKind)) == kLitEob) { odd = true; break; }   // no code here / end of block
+        const uint32_t v1 = simt::funnel_r(rr.w1, rr.w2, rr.bo);
+        const bool     is_len = (e & kLitIsLen) != 0u;
+        const uint32_t cl   = (e >> 11) & 15u;
+        const uint32_t xb   = (e >> 8) & 7u;                        // 0 for a literal
+        const uint32_t val  = (e & 255u) + low_bits(v0 >> cl, xb);  // byte, or length - 3
+        const uint32_t use1 = cl + xb;
+        const uint32_t v2   = simt::funnel_r(v0, v1, use1);         // the 32 bits after this symbol
+        uint32_t       x    = lit[is_len ? dist_at + (v2 & (kDistRoot - 1)) : (v2 & (kLitRoot - 1))];
+        if (is_len && (x & kDistSub))
+          x = dist[kDistRoot + (x & 0x1FFu) + low_bits(v2 >> kDistRootBits, (x >> 11) & 15u)];
+        if (is_len && x == 0u) { odd = true; break; }               // no distance code here
+        const uint32_t xcl = (x >> 11) & 15u;
+        const uint32_t dxb = (x >> 7) & 15u;
+        const uint32_t d1  = ((x & 3u) << dxb) + low_bits(v2 >> xcl, dxb);          // distance - 1
+        const bool     two = (x & (kLitIsLen | kLitKind)) == 0u && x >= 0x0800u && r + use1 < lim;   // a second literal joins
+        // selects, not branches: literal lanes and match lanes sit side by side in every warp
+        const uint32_t tok_m = kTokIsMatch | (d1 << 9) | (val + 3u);
+        const uint32_t tok_l = simt::byte_perm(val, x, 0x1140u) + (two ? (2u << 24) : (1u << 24));   // the second byte only counts when two
+        const uint32_t use2  = is_len ? xcl + dxb : (two ? xcl : 0u);
+        seg[ti++] = is_len ? tok_m : tok_l;
+        r += use1 + use2;
+        rr.consume(use1 + use2);
+      } while ((ti & (kCpTokens - 1u)) != 0u && r < fast_limit);
+      if (odd) break;
+    }
+    // ---- one careful step: the ends of a phase, of the input and of the block, failures
+    if (r >= lim) {
+      if (!warming) break;
+      warming = false; m0 = ti; r0 = r; lim = limit;              // the warm-up is over: this token is the first kept
+      continue;
+    }
+    uint32_t s = LS_FULL, tok = 0, used = 0;
+    if (ti != kSpecCap) {
+      if ((ti & (kCpTokens - 1u)) == 0u) cps[ti / kCpTokens] = (uint16_t)(r - org);
+      s = decode_token(lit, dist, rr, endr > r ? endr - r : 0u, lim - r, tok, used);
+    }
+    if (s == LS_OK) {
+      seg[ti++] = tok;
       r += used;
       rr.consume(used);
+      continue;
     }
-    if (stat == LS_FULL) break;
-    // ---- one careful step: the ends of the sub-sequence, the input and the block, failures
-    if (r >= limit) break;
-    if (tp == tend) { stat = LS_FULL; break; }
-    if (r >= next_cp) {
-      *cpp++ = (uint16_t)((r - next_cp) | ((uint32_t)(tp - seg) << 6));
-      next_cp += kCpBits;
+    if (warming) {                                                // start again, blind, where the sub-sequence begins
+      warming = false; lim = limit; org = start; r = start; r0 = start; m0 = 0; ti = 0;
+      rr.drain();
+      rr.seek(words, wend, bw, r, ring_lane);
+      continue;
     }
-    uint32_t tok, used;
-    const uint32_t s = decode_token(lit, dist, rr, endr > r ? endr - r : 0u, true, tok, used);
-    if (s != LS_OK) {
-      stat = s;
-      if (s == LS_EOB) r += used;
-      break;
-    }
-    *tp++ = tok;
-    r += used;
-    rr.consume(used);
+    stat = s;
+    if (s == LS_EOB) r += used;
+    break;
   }
   rr.drain();
-  if (stop_lane && (stat == LS_EOB || (stat & 0xFFu) == LS_FAIL)) simt::atomic_min_shared(stop_lane, lane);
-  const uint32_t t = (uint32_t)(tp - seg);
-  tj.land = r; tj.stat = stat; tj.n = t; tj.m = 0; tj.nf = 0; tj.T = r0; tj.ncp = (uint32_t)(cpp - cps);
-  tj.s_land = r; tj.s_stat = stat; tj.s_n = t;
+  tj.land = r; tj.stat = stat; tj.n = ti; tj.m = m0; tj.nf = 0; tj.T = r0; tj.org = org;
+  tj.s_land = r; tj.s_stat = stat; tj.s_n = ti;
 }
 
 // fix-up pass: decode from the true start `T` until the speculative trajectory is met at a checkpoint
 DEFL_DEV void lane_redo(const uint16_t* lit, const uint16_t* dist, const uint32_t* words, uint32_t wend,
-                        uint32_t bw, uint32_t start, uint32_t limit, uint32_t endr, uint32_t* fix,
+                        uint32_t bw, uint32_t limit, uint32_t endr, uint32_t* fix,
                         const uint16_t* cps, uint32_t T, LaneTraj& tj) {
   SubReader br;
   br.w = words; br.wend = wend;
   br.seek(bw, T);
-  uint32_t r = T, f = 0;
-  uint32_t k = (T - start + kCpBits - 1u) / kCpBits;
-  const uint32_t ncp = tj.ncp;
-  uint32_t c = k < ncp ? cps[k] : 0u;
-  uint32_t target = k < ncp ? start + k * kCpBits + (c & 63u) : 0xFFFFFFFFu;
+  uint32_t r = T, f = 0, k = 0;
+  const uint32_t ncp = (tj.s_n + kCpTokens - 1u) / kCpTokens;    // checkpoints 0 .. ncp - 1 were written
+  uint32_t target = k < ncp ? tj.org + cps[k] : 0xFFFFFFFFu;
   tj.T = T;
   for (;;) {
     while (r > target) {
       k++;
-      c = k < ncp ? cps[k] : 0u;
-      target = k < ncp ? start + k * kCpBits + (c & 63u) : 0xFFFFFFFFu;
+      target = k < ncp ? tj.org + cps[k] : 0xFFFFFFFFu;
     }
-    if (r == target) {            // met the speculative trajectory: its tokens from c >> 6 on are true
-      tj.m = c >> 6; tj.nf = f;
+    if (r == target) {            // met the speculative trajectory: its tokens from kCpTokens * k on are true
+      tj.m = kCpTokens * k; tj.nf = f;
       tj.land = tj.s_land; tj.stat = tj.s_stat; tj.n = tj.s_n;
       return;
     }
@@ -331,7 +332,7 @@ DEFL_DEV void lane_redo(const uint16_t* lit, const uint16_t* dist, const uint32_
       stat = LS_FULL;
     } else {
       uint32_t tok, used;
-      const uint32_t s = decode_token(lit, dist, br, endr > r ? endr - r : 0u, false, tok, used);
+      const uint32_t s = decode_token(lit, dist, br, endr > r ? endr - r : 0u, limit - r, tok, used);
       if (s == LS_OK) {
         fix[f++] = tok;
         r += used;
@@ -628,7 +629,7 @@ DEFL_DEV uint32_t decode_window(WarpSmem& sm, const WarpScratch& sc, int lane, c
   const uint32_t softr = soft64 > (uint64_t)endr ? endr : (uint32_t)soft64;        // window-relative soft end
   const uint32_t remaining = softr - rel0;
   uint32_t S = (remaining + 31u) / 32u;
-  S = (S + kCpBits - 1u) / kCpBits * kCpBits;
+  S = (S + kSubGrain - 1u) / kSubGrain * kSubGrain;
   S = S < kSubMin ? kSubMin : (S > kSubMax ? kSubMax : S);
 
   const uint32_t start = rel0 + (uint32_t)lane * S;
@@ -639,15 +640,13 @@ DEFL_DEV uint32_t decode_window(WarpSmem& sm, const WarpScratch& sc, int lane, c
   uint16_t* cps = sc.cps + (uint32_t)lane * kCpPerLane;
 
   LaneTraj tj;
-  tj.land = start; tj.stat = LS_NONE; tj.n = 0; tj.m = 0; tj.nf = 0; tj.T = start; tj.ncp = 0;
+  tj.land = start; tj.stat = LS_NONE; tj.n = 0; tj.m = 0; tj.nf = 0; tj.T = start; tj.org = start;
   tj.s_land = start; tj.s_stat = LS_NONE; tj.s_n = 0;
   const uint32_t warm = (lane >= 1 && active) ? (warm_bits < S ? warm_bits : S) : 0u;      // lane 0 starts on a known boundary
   // the resolver's stage is idle during the speculative pass: it holds the lanes' input rings
-  if (lane == 0) sm.stop_lane = 32u;
   simt::syncwarp(kFull);
   if (active) lane_spec(sm.lit, sm.dist, words, wend, bw, start, limit, endr, seg, cps, tj, warm,
-                        reinterpret_cast<uint32_t*>(sm.stage) + lane * 4,
-                        nullptr, (uint32_t)lane);   // early stop past a lower lane's end of block: tried, slower
+                        reinterpret_cast<uint32_t*>(sm.stage) + lane * 4);
   simt::syncwarp(kFull);
 
   // fix-up rounds until every lane starts where its predecessor ended
@@ -657,7 +656,7 @@ DEFL_DEV uint32_t decode_window(WarpSmem& sm, const WarpScratch& sc, int lane, c
     const uint32_t pstat = simt::shfl_up(kFull, tj.stat, 1);
     const bool need = lane >= 1 && active && pstat == LS_OK && pland != tj.T;
     if (!simt::any(kFull, need)) break;
-    if (need) lane_redo(sm.lit, sm.dist, words, wend, bw, start, limit, endr, fix, cps, pland, tj);
+    if (need) lane_redo(sm.lit, sm.dist, words, wend, bw, limit, endr, fix, cps, pland, tj);
     simt::syncwarp(kFull);
   }
 
