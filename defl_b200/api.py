@@ -107,6 +107,19 @@ def lib():
     L.infl_set_pipeline_shape.argtypes = [i32]
     L.infl_set_engine.restype = i32
     L.infl_set_engine.argtypes = [i32]
+    # include/defl/infl_wrap.h (declared here so that a caller passing plain integers gets 64-bit pointers)
+    L.infl_gzip_batch.restype = i32
+    L.infl_gzip_batch.argtypes = [vp, sz, i32, vp]
+    L.infl_crc32_batch.restype = i32
+    L.infl_crc32_batch.argtypes = [vp, sz, i32, vp]
+    L.infl_zip_list.restype = i32
+    L.infl_zip_list.argtypes = [vp, u64, i32, vp, sz, vp]
+    L.infl_zip_extract.restype = i32
+    L.infl_zip_extract.argtypes = [vp, u64, vp, sz, vp, i32, vp]
+    L.infl_png_batch.restype = i32
+    L.infl_png_batch.argtypes = [vp, sz, i32, vp]
+    L.infl_png_unfilter_device.restype = i32
+    L.infl_png_unfilter_device.argtypes = [vp, vp, vp, vp, vp, sz, vp, vp]
     _lib = L
     return L
 

@@ -1205,7 +1205,7 @@ UNZ_EXPORT int infl_batch_decode_device(const infl_batch_item_t* d_items, const 
 
 // ---- infl_batch_decode_device_static: the batch kernel with NO allocation anywhere on the call path ----------
 // The token scratch of the one-warp-per-stream kernel lives in a file-scope device array instead of a caller's
-// workspace: kStaticWarps warps' worth (37 CTAs x 4 warps = one warp per SM of a B200), about 37.6 MiB that every
+// workspace: kStaticWarps warps' worth (37 CTAs x 4 warps = one warp per SM of a B200), about 38.2 MiB that every
 // GPU which loads this library holds until the process exits.  In HOST code `g_static_ws` is only a stand-in for
 // the symbol, not a device address: the address comes from cudaGetSymbolAddress, once per device, with that
 // device current, and that pointer is what the kernel gets.

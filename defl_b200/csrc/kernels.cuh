@@ -99,7 +99,7 @@ constexpr size_t pipeline_smem_bytes() { return sizeof(Slot) * D * SL + sizeof(W
 // scratch and pulls streams from the ticket counter.
 template <int WARPS>
 #ifndef DEFL_WARP_CTAS_PER_SM
-#define DEFL_WARP_CTAS_PER_SM 8      // x 4 warps: 32 resident warps per SM at 64 registers (10 -> 48 registers spills, 6 gains nothing)
+#define DEFL_WARP_CTAS_PER_SM 7      // x 4 warps: 28 resident warps per SM at 72 registers (8 -> 64 registers: the speculative loop recomputes what it cannot hold, 149 GB/s; 6 -> 80 registers: 191; profiles/README.md)
 #endif
 __global__ void __launch_bounds__(WARPS * 32, DEFL_WARP_CTAS_PER_SM)
 inflate_warp_kernel(const infl_batch_item_t* __restrict__ items, const uint32_t* __restrict__ order,

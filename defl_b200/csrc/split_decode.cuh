@@ -242,8 +242,11 @@ DEFL_DEV uint64_t fixed_probe_lane(const uint16_t* lit, const uint16_t* dist, co
 }
 
 #ifdef __CUDACC__
+#ifndef DEFL_SPLIT_CTAS_PER_SM
+#define DEFL_SPLIT_CTAS_PER_SM 7     // x 4 warps, as the batch kernel (kernels.cuh)
+#endif
 template <bool COUNT, int WARPS>
-__global__ void __launch_bounds__(WARPS * 32, 32 / WARPS)
+__global__ void __launch_bounds__(WARPS * 32, DEFL_SPLIT_CTAS_PER_SM)
 split_chunk_kernel(const SplitStreamDesc* __restrict__ streams, const uint64_t* __restrict__ cand,
                    const SplitJob* __restrict__ jobs, uint32_t njobs, uint16_t* __restrict__ sym,
                    SplitChunkOut* __restrict__ outs, unsigned int* __restrict__ ticket,

@@ -225,81 +225,88 @@ struct LaneTraj {
 //    lookup goes to lit[] or dist[] by index, not by branch), a 32-bit token index.
 DEFL_DEV void lane_spec(const uint16_t* lit, const uint16_t* dist, const uint32_t* words, uint32_t wend,
                         uint32_t bw, uint32_t start, uint32_t limit, uint32_t endr, uint32_t* seg,
-                        uint16_t* cps, LaneTraj& tj, uint32_t warm, uint32_t* ring_lane) {
+                        uint16_t* cps, LaneTraj& tj, uint32_t warm, uint32_t* ring_lane, bool active) {
+  // ALL 32 lanes come here (an inactive one only keeps the others company at the two barriers below).
   RingReader rr;
   uint32_t   org = start - warm;
   uint32_t   r = org, r0 = start, m0 = 0, ti = 0, stat = LS_OK;
-  uint32_t   lim = warm ? start : limit;                       // the end of the current phase
-  bool       warming = warm != 0u;
-  rr.seek(words, wend, bw, r, ring_lane);
+  if (active) rr.seek(words, wend, bw, r, ring_lane);
   const uint32_t  endr64  = endr >= 64u ? endr - 64u : 0u;
   const uint32_t  dist_at = (uint32_t)(dist - lit);            // dist[] follows lit[] in shared memory
-  for (;;) {
-    const uint32_t fast_limit = lim < endr64 ? lim : endr64;
-    // ---- fast loop: a checkpoint, then up to kCpTokens tokens
-    while (r < fast_limit && ti < kSpecCap) {
-      if ((ti & (kCpTokens - 1u)) == 0u) cps[ti / kCpTokens] = (uint16_t)(r - org);
-      bool odd = false;                                           // something that is not a token
+  // Two phases, the warm-up and the sub-sequence itself, through the same loop body.  The lanes start each phase
+  // TOGETHER (lane 0 has no warm-up and waits): a lane that went on alone would run the loop on its own, and every
+  // trip of it would cost the warp a full pass.
 #pragma unroll 1
-      do {
-        const uint32_t v0 = simt::funnel_r(rr.w0, rr.w1, rr.bo);
-        uint32_t       e  = lit[v0 & (kLitRoot - 1)];
-        if ((e & (kLitIsLen | kLitKind)) == kLitSub)
-          e = lit[kLitRoot + (e & 0x1FFu) + low_bits(v0 >> kLitRootBits, (e >> 11) & 15u)];
-        if (e < 0x0800u || (e & (kLitIsLen | kLitKind)) == kLitEob) { odd = true; break; }   // no code here / end of block
-        const uint32_t v1 = simt::funnel_r(rr.w1, rr.w2, rr.bo);
-        const bool     is_len = (e & kLitIsLen) != 0u;
-        const uint32_t cl   = (e >> 11) & 15u;
-        const uint32_t xb   = (e >> 8) & 7u;                        // 0 for a literal
-        const uint32_t val  = (e & 255u) + low_bits(v0 >> cl, xb);  // byte, or length - 3
-        const uint32_t use1 = cl + xb;
-        const uint32_t v2   = simt::funnel_r(v0, v1, use1);         // the 32 bits after this symbol
-        uint32_t       x    = lit[is_len ? dist_at + (v2 & (kDistRoot - 1)) : (v2 & (kLitRoot - 1))];
-        if (is_len && (x & kDistSub))
-          x = dist[kDistRoot + (x & 0x1FFu) + low_bits(v2 >> kDistRootBits, (x >> 11) & 15u)];
-        if (is_len && x == 0u) { odd = true; break; }               // no distance code here
-        const uint32_t xcl = (x >> 11) & 15u;
-        const uint32_t dxb = (x >> 7) & 15u;
-        const uint32_t d1  = ((x & 3u) << dxb) + low_bits(v2 >> xcl, dxb);          // distance - 1
-        const bool     two = (x & (kLitIsLen | kLitKind)) == 0u && x >= 0x0800u && r + use1 < lim;   // a second literal joins
-        // selects, not branches: literal lanes and match lanes sit side by side in every warp
-        const uint32_t tok_m = kTokIsMatch | (d1 << 9) | (val + 3u);
-        const uint32_t tok_l = simt::byte_perm(val, x, 0x1140u) + (two ? (2u << 24) : (1u << 24));   // the second byte only counts when two
-        const uint32_t use2  = is_len ? xcl + dxb : (two ? xcl : 0u);
-        seg[ti++] = is_len ? tok_m : tok_l;
-        r += use1 + use2;
-        rr.consume(use1 + use2);
-      } while ((ti & (kCpTokens - 1u)) != 0u && r < fast_limit);
-      if (odd) break;
+  for (uint32_t phase = 0; phase < 2u; phase++) {
+    simt::syncwarp(kFull);
+    const uint32_t lim = phase == 0u ? start : limit;          // the end of this phase
+    const uint32_t fast_limit = lim < endr64 ? lim : endr64;
+    if (active && (phase == 1u || warm != 0u)) {
+      for (;;) {
+        // ---- fast loop: a checkpoint, then up to kCpTokens tokens
+        while (r < fast_limit && ti < kSpecCap) {
+          if ((ti & (kCpTokens - 1u)) == 0u) cps[ti / kCpTokens] = (uint16_t)(r - org);
+          bool odd = false;                                           // something that is not a token
+#pragma unroll 1
+          do {
+            const uint32_t v0 = simt::funnel_r(rr.w0, rr.w1, rr.bo);
+            uint32_t       e  = lit[v0 & (kLitRoot - 1)];
+            if ((e & (kLitIsLen | kLitKind)) == kLitSub)
+              e = lit[kLitRoot + (e & 0x1FFu) + low_bits(v0 >> kLitRootBits, (e >> 11) & 15u)];
+            if (e < 0x0800u || (e & (kLitIsLen | kLitKind)) == kLitEob) { odd = true; break; }   // no code here / end of block
+            const uint32_t v1 = simt::funnel_r(rr.w1, rr.w2, rr.bo);
+            const bool     is_len = (e & kLitIsLen) != 0u;
+            const uint32_t cl   = (e >> 11) & 15u;
+            const uint32_t xb   = (e >> 8) & 7u;                        // 0 for a literal
+            const uint32_t val  = (e & 255u) + low_bits(v0 >> cl, xb);  // byte, or length - 3
+            const uint32_t use1 = cl + xb;
+            const uint32_t v2   = simt::funnel_r(v0, v1, use1);         // the 32 bits after this symbol
+            uint32_t       x    = lit[is_len ? dist_at + (v2 & (kDistRoot - 1)) : (v2 & (kLitRoot - 1))];
+            if (is_len && (x & kDistSub))
+              x = dist[kDistRoot + (x & 0x1FFu) + low_bits(v2 >> kDistRootBits, (x >> 11) & 15u)];
+            if (is_len && x == 0u) { odd = true; break; }               // no distance code here
+            const uint32_t xcl = (x >> 11) & 15u;
+            const uint32_t dxb = (x >> 7) & 15u;
+            const uint32_t d1  = ((x & 3u) << dxb) + low_bits(v2 >> xcl, dxb);          // distance - 1
+            const bool     two = (x & (kLitIsLen | kLitKind)) == 0u && x >= 0x0800u && r + use1 < lim;   // a second literal joins
+            // selects, not branches: literal lanes and match lanes sit side by side in every warp
+            const uint32_t tok_m = kTokIsMatch | (d1 << 9) | (val + 3u);
+            const uint32_t tok_l = simt::byte_perm(val, x, 0x1140u) + (two ? (2u << 24) : (1u << 24));   // the second byte only counts when two
+            const uint32_t use2  = is_len ? xcl + dxb : (two ? xcl : 0u);
+            seg[ti++] = is_len ? tok_m : tok_l;
+            r += use1 + use2;
+            rr.consume(use1 + use2);
+          } while ((ti & (kCpTokens - 1u)) != 0u && r < fast_limit);
+          if (odd) break;
+        }
+        // ---- one careful step: the ends of the phase, of the input and of the block, failures
+        if (r >= lim) break;
+        uint32_t s = LS_FULL, tok = 0, used = 0;
+        if (ti != kSpecCap) {
+          if ((ti & (kCpTokens - 1u)) == 0u) cps[ti / kCpTokens] = (uint16_t)(r - org);
+          s = decode_token(lit, dist, rr, endr > r ? endr - r : 0u, lim - r, tok, used);
+        }
+        if (s == LS_OK) {
+          seg[ti++] = tok;
+          r += used;
+          rr.consume(used);
+          continue;
+        }
+        if (phase == 0u) {                                          // start again, blind, where the sub-sequence begins
+          org = start; r = start; ti = 0;
+          rr.drain();
+          rr.seek(words, wend, bw, r, ring_lane);
+        } else {
+          stat = s;
+          if (s == LS_EOB) r += used;
+        }
+        break;
+      }
     }
-    // ---- one careful step: the ends of a phase, of the input and of the block, failures
-    if (r >= lim) {
-      if (!warming) break;
-      warming = false; m0 = ti; r0 = r; lim = limit;              // the warm-up is over: this token is the first kept
-      continue;
-    }
-    uint32_t s = LS_FULL, tok = 0, used = 0;
-    if (ti != kSpecCap) {
-      if ((ti & (kCpTokens - 1u)) == 0u) cps[ti / kCpTokens] = (uint16_t)(r - org);
-      s = decode_token(lit, dist, rr, endr > r ? endr - r : 0u, lim - r, tok, used);
-    }
-    if (s == LS_OK) {
-      seg[ti++] = tok;
-      r += used;
-      rr.consume(used);
-      continue;
-    }
-    if (warming) {                                                // start again, blind, where the sub-sequence begins
-      warming = false; lim = limit; org = start; r = start; r0 = start; m0 = 0; ti = 0;
-      rr.drain();
-      rr.seek(words, wend, bw, r, ring_lane);
-      continue;
-    }
-    stat = s;
-    if (s == LS_EOB) r += used;
-    break;
+    if (phase == 0u) { m0 = ti; r0 = r; }                            // the first kept token
   }
-  rr.drain();
+  if (active) rr.drain();
+  if (!active) return;
   tj.land = r; tj.stat = stat; tj.n = ti; tj.m = m0; tj.nf = 0; tj.T = r0; tj.org = org;
   tj.s_land = r; tj.s_stat = stat; tj.s_n = ti;
 }
@@ -645,8 +652,8 @@ DEFL_DEV uint32_t decode_window(WarpSmem& sm, const WarpScratch& sc, int lane, c
   const uint32_t warm = (lane >= 1 && active) ? (warm_bits < S ? warm_bits : S) : 0u;      // lane 0 starts on a known boundary
   // the resolver's stage is idle during the speculative pass: it holds the lanes' input rings
   simt::syncwarp(kFull);
-  if (active) lane_spec(sm.lit, sm.dist, words, wend, bw, start, limit, endr, seg, cps, tj, warm,
-                        reinterpret_cast<uint32_t*>(sm.stage) + lane * 4);
+  lane_spec(sm.lit, sm.dist, words, wend, bw, start, limit, endr, seg, cps, tj, warm,
+            reinterpret_cast<uint32_t*>(sm.stage) + lane * 4, active);
   simt::syncwarp(kFull);
 
   // fix-up rounds until every lane starts where its predecessor ended

@@ -94,7 +94,7 @@ UNZ_EXPORT int infl_batch_decode_device(const infl_batch_item_t *d_items, const 
    reference; it was added for callers that cannot call
    cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  The
    kernel's token scratch is a file-scope `static __device__` array inside the library (about
-   37.6 MiB: 148 warps' worth, held by every GPU that loads the library until the process exits), so
+   38.2 MiB: 148 warps' worth, held by every GPU that loads the library until the process exits), so
    no workspace is passed and neither cudaMalloc / cudaFree nor any allocating library routine is
    called.  Limits: n <= INFL_BATCH_STATIC_MAX_STREAMS per call (more => UNZ_ERR and a message in
    infl_last_error(); use infl_batch_decode_device), 148 warps work at a time however large the GPU,
