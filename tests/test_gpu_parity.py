@@ -629,3 +629,42 @@ def test_chunk_lists_scattered_host_pieces_and_device_pieces(gpu_lib):
         raw = streams[k % len(streams)][0]
         assert int(g["code"]) == 0 and int(g["outlen"]) == len(raw), (k, int(g["info"]) >> 8)
         assert dsts[k][: len(raw)].cpu().numpy().tobytes() == raw, k
+
+
+@pytest.mark.gpu
+def test_degenerate_codes_and_window_shapes(gpu_lib):
+    """The shapes that stress the speculative pass's bookkeeping: codes of one or two bits (a lane's token segment fills
+    long before its sub-sequence ends, warm-up tokens included), Huffman-only / RLE / fixed-code streams, blocks of a
+    few hundred bytes (sub-sequences shorter than the warm-up), every size around the window and checkpoint grains,
+    tight and exact output capacities.  Against the oracle port: bytes, lengths, codes, Adler-32."""
+    d = gpu_lib
+    rng = np.random.default_rng(77)
+    payloads = []
+    for n in (1, 2, 3, 7, 8, 9, 63, 64, 65, 255, 256, 257, 1023, 1024, 1025, 4095, 4096, 4097, 65535, 65536, 1 << 20):
+        payloads.append(bytes(n))                                               # one symbol: 1-bit codes
+        payloads.append(bytes(rng.integers(0, 2, n, dtype=np.uint8)))           # two symbols
+        payloads.append(bytes(rng.integers(0, 4, n, dtype=np.uint8) * 85))      # four symbols: 2-bit codes
+        payloads.append(bytes(rng.integers(0, 256, n, dtype=np.uint8)))         # incompressible
+    datas, caps = [], []
+    for p in payloads:
+        for strategy in (zlib.Z_HUFFMAN_ONLY, zlib.Z_RLE, zlib.Z_FIXED, zlib.Z_DEFAULT_STRATEGY):
+            c = zlib.compressobj(6, zlib.DEFLATED, -15, 8, strategy)
+            datas.append(c.compress(p) + c.flush()); caps.append(len(p))
+    # many small blocks: a full flush every 100 .. 700 bytes of text-like data
+    words = [bytes(rng.integers(97, 123, int(k), dtype=np.uint8)) for k in rng.integers(2, 9, 400)]
+    text = b" ".join(words[int(i)] for i in rng.integers(0, 400, 60000))
+    c = zlib.compressobj(6, zlib.DEFLATED, -15)
+    parts, at = [], 0
+    while at < len(text):
+        k = int(rng.integers(100, 700))
+        parts.append(c.compress(text[at:at + k]) + c.flush(zlib.Z_FULL_FLUSH)); at += k
+    parts.append(c.flush())
+    datas.append(b"".join(parts)); caps.append(len(text))
+    # capacities one short, exact, and with slack
+    more_d, more_c = [], []
+    for dd, cc in list(zip(datas, caps))[::7]:
+        if cc > 1:
+            more_d += [dd, dd]; more_c += [cc - 1, cc + 100]
+    datas += more_d; caps += more_c
+    res, outs = d.infl_buf_batch(datas, caps, 0)
+    _check_against_port(d, res, outs, datas, caps, 0, "degenerate")
