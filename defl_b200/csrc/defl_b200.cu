@@ -533,10 +533,30 @@ int split_decode_many(Engine* E, const SplitInput* in, size_t nin, int flags, vo
       split_chunk_kernel<true, kWarpsPerCta><<<grid, kWarpsPerCta * 32, smem, st>>>(
           d_sd, static_cast<uint64_t*>(SB.d_cand.p), static_cast<SplitJob*>(SB.d_jobs.p), njobs,
           sym, static_cast<SplitChunkOut*>(SB.d_outs.p), ticket, scratch, d_tok);
-    else
+    else {
+      // chunks whose tokens were kept: the resolver alone, in its own kernel (more warps per SM, see split_replay_kernel);
+      // the others (over their token budget): decoded again by the full kernel, which skips the replayed ones
+      uint32_t nreplay = 0;
+      for (uint32_t j = 0; j < njobs; j++) nreplay += jobs[j].ntok != kNoTokens;
+      if (nreplay) {
+        static std::atomic<int> replay_ctas[kMaxDevices];
+        if (!replay_ctas[E->dev]) {
+          int occ = 0;
+          CU_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, split_replay_kernel<kWarpsPerCta>, kWarpsPerCta * 32, 0), "occupancy query");
+          replay_ctas[E->dev] = occ > 0 ? occ : 1;
+        }
+        const unsigned rgrid = (unsigned)std::max<uint32_t>(1, std::min<uint32_t>((uint32_t)(E->sms * replay_ctas[E->dev]), (njobs + kWarpsPerCta - 1) / kWarpsPerCta));
+        split_replay_kernel<kWarpsPerCta><<<rgrid, kWarpsPerCta * 32, 0, st>>>(
+            static_cast<SplitJob*>(SB.d_jobs.p), njobs, sym, static_cast<SplitChunkOut*>(SB.d_outs2.p), ticket, d_tok);
+        CU_TRY(cudaGetLastError(), "split_replay_kernel launch");
+        g_launches.fetch_add(1, std::memory_order_relaxed);
+      }
+      if (nreplay == njobs) return UNZ_OK;
+      if (nreplay) CU_TRY(cudaMemsetAsync(ticket, 0, sizeof(unsigned int), st), "cudaMemsetAsync(ticket)");
       split_chunk_kernel<false, kWarpsPerCta><<<grid, kWarpsPerCta * 32, smem, st>>>(
           d_sd, static_cast<uint64_t*>(SB.d_cand.p), static_cast<SplitJob*>(SB.d_jobs.p), njobs,
-          sym, static_cast<SplitChunkOut*>(SB.d_outs2.p), ticket, scratch, d_tok);
+          sym, static_cast<SplitChunkOut*>(SB.d_outs2.p), ticket, scratch, nullptr);
+    }
     CU_TRY(cudaGetLastError(), "split_chunk_kernel launch");
     g_launches.fetch_add(1, std::memory_order_relaxed);
     return UNZ_OK;
@@ -554,7 +574,16 @@ int split_decode_many(Engine* E, const SplitInput* in, size_t nin, int flags, vo
   // ---- per stream, the chain of true chunks from its first block to its final block
   // A chunk that starts inside a block (MODE_FIXED_MID) learns from its predecessor whether that block is the
   // stream's last one; if it is, the chunk ends at that block's end-of-block code (eob_* of its record).
-  struct ChainItem { uint32_t stream, cand; uint64_t off; uint32_t bytes, ntok, start_final; bool ends; };   // off = offset inside the stream
+  // off = offset inside the stream; tok0 / sub: a chunk whose tokens were kept is replayed in pieces (cut where the COUNT
+  // pass marked the end of a decode window about every kPieceBytes of output): tok0 = first token of the piece, sub = it
+  // is not the chunk's first piece.  Every piece is a chunk of its own for the C and D passes -- the 32 KiB before it are
+  // unknown to its replay and become markers -- so that one long chunk no longer sets the time of the C pass.
+  struct ChainItem { uint32_t stream, cand; uint64_t off; uint32_t bytes, ntok, start_final; bool ends; uint32_t tok0; bool sub; };
+  // Pieces pay when the chunks alone do not fill the replay kernel (one big stream: 4700 chunks of uneven length for
+  // ~7100 warps, C pass 10.5 -> 5.2 ms per GiB); a batch of many split members has chunks enough, and there the extra
+  // windows only cost (mixed workload 83.5 -> 75.9 GB/s with pieces).  DEFL_SPLIT_PIECES: 0 never, 1 always, 2 by that rule.
+  const uint32_t pieces_mode = env_u32("DEFL_SPLIT_PIECES", 2, 0, 2);
+  const bool pieces = pieces_mode == 1u || (pieces_mode == 2u && (uint64_t)ncand * 2u <= (uint64_t)E->sms * 48u * 3u);
   std::vector<ChainItem> chain;
   std::vector<uint64_t>  off;                                      // per stream nchunk + 1 entries
   std::vector<uint64_t>  end_bit(ns, 0);
@@ -578,8 +607,22 @@ int split_decode_many(Engine* E, const SplitInput* in, size_t nin, int flags, vo
       if (fin == FIN_YES && k != 0 && !o[k].has_eob && o[k].status != CH_LINKED) { ok = false; break; }
       const uint32_t bytes = ends_here ? o[k].eob_bytes : o[k].out_bytes;
       if (bytes >= 0x80000000u) { ok = false; break; }   // resolve_tokens<uint16_t> compares chunk-relative positions as int32
-      chain.push_back({i, k, total, bytes, ends_here ? o[k].eob_ntok : o[k].ntok, k == 0 ? (uint32_t)FIN_NO : fin, ends_here});
-      off.push_back(total);
+      const uint32_t ntok_k = ends_here ? o[k].eob_ntok : o[k].ntok;
+      const uint32_t sf = k == 0 ? (uint32_t)FIN_NO : fin;
+      uint32_t p_pos = 0, p_tok = 0;
+      bool     sub = false;
+      if (pieces && ntok_k != defl::kNoTokens) {
+        for (uint32_t m = 0; m < o[k].npiece && m < defl::kMaxPieces; m++) {
+          const uint32_t mp = o[k].piece_pos[m], mt = o[k].piece_tok[m];
+          if (mp >= bytes || mt >= ntok_k || bytes - mp < kWinBytes) break;       // every piece but a stream's last holds a whole window
+          if (mp - p_pos < kWinBytes || mt <= p_tok) continue;
+          chain.push_back({i, k, total + p_pos, mp - p_pos, mt - p_tok, sf, false, p_tok, sub});
+          off.push_back(total + p_pos);
+          p_pos = mp; p_tok = mt; sub = true;
+        }
+      }
+      chain.push_back({i, k, total + p_pos, bytes - p_pos, ntok_k == defl::kNoTokens ? ntok_k : ntok_k - p_tok, sf, ends_here, p_tok, sub});
+      off.push_back(total + p_pos);
       total += bytes;
       if (total > in[i].dstlen || total > 0xFFFFFFFFull) { ok = false; break; }
       if (ends_here) { end_bit[i] = o[k].eob_bit; break; }
@@ -608,6 +651,8 @@ int split_decode_many(Engine* E, const SplitInput* in, size_t nin, int flags, vo
 
   // ---- C: the chains decode into 16-bit symbols at final offsets; largest chunk first (the pass ends when
   // its slowest warp does)
+  if (jobs.size() < nchunk) jobs.resize(nchunk);
+  if (SB.d_jobs.reserve((size_t)nchunk * sizeof(SplitJob)) || SB.d_outs2.reserve((size_t)nchunk * sizeof(SplitChunkOut))) return UNZ_ERR;
   std::vector<uint32_t> perm(nchunk);
   std::iota(perm.begin(), perm.end(), 0u);
   auto out_of = [&](uint32_t c) -> const SplitChunkOut& { return outs[sd[chain[c].stream].cand_base + chain[c].cand]; };
@@ -621,8 +666,8 @@ int split_decode_many(Engine* E, const SplitInput* in, size_t nin, int flags, vo
     const SplitStreamDesc& d = sd[ci.stream];
     jobs[j].stream = ci.stream; jobs[j].start_final = ci.start_final; jobs[j].cand = ci.cand;
     jobs[j].cap = ci.bytes; jobs[j].out_off = d.sym_base + ci.off;
-    jobs[j].tok_off = d.tok_base + (uint64_t)tok_per_byte * (cand[d.cand_base + ci.cand] >> 3);
-    jobs[j].tok_cap = 0;
+    jobs[j].tok_off = d.tok_base + (uint64_t)tok_per_byte * (cand[d.cand_base + ci.cand] >> 3) + ci.tok0;
+    jobs[j].tok_cap = (ci.sub || ci.cand != 0u) ? 32768u : 0u;                 // replay: symbols of unknown history
     jobs[j].ntok = d_tok ? ci.ntok : kNoTokens;
   }
   if (SB.d_sym.reserve((size_t)sym_total * 2 + 64) || SB.d_off.reserve(off.size() * 8) ||

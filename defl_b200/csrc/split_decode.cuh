@@ -26,6 +26,11 @@ namespace defl {
 enum : uint32_t { CH_LINKED = 0, CH_FINAL = 1, CH_FAIL = 2, CH_REPLAYED = 3 };   // CH_FAIL | reason << 8
 constexpr uint32_t kNoTokens = 0xFFFFFFFFu;
 
+constexpr uint32_t kMaxPieces  = 7;         // a chunk is replayed as up to 8 pieces
+#ifndef DEFL_PIECE_BYTES
+#define DEFL_PIECE_BYTES 98304
+#endif
+constexpr uint32_t kPieceBytes = DEFL_PIECE_BYTES;
 struct SplitChunkOut {
   uint64_t end_bit;     // stream-relative bit where the chunk stopped (a block boundary unless it failed)
   uint32_t status;      // CH_*
@@ -38,6 +43,11 @@ struct SplitChunkOut {
   uint32_t eob_bytes;   //   bytes produced up to there
   uint32_t eob_ntok;    //   tokens kept up to there (or kNoTokens)
   uint64_t eob_bit;     //   stream-relative bit after its end-of-block code
+  // COUNT, tokens kept: places where the chunk can be cut for the replay (ends of decode windows about
+  // kPieceBytes of output apart): the first piece_tok[m] tokens produce exactly piece_pos[m] bytes
+  uint32_t npiece;
+  uint32_t piece_tok[kMaxPieces];
+  uint32_t piece_pos[kMaxPieces];
 };
 enum : uint32_t { FIN_NO = 0, FIN_YES = 1, FIN_UNKNOWN = 2 };
 enum : uint32_t { MODE_BLOCK_STARTS = 0, MODE_FIXED_MID = 1 };   // SplitStreamDesc::mode: what the candidates are
@@ -77,7 +87,7 @@ struct SplitJob {
   uint32_t cap;         // DECODE: exactly the bytes the COUNT pass reported
   uint64_t out_off;     // DECODE: offset of the chunk's first symbol
   uint64_t tok_off;     // where the chunk's tokens are kept (COUNT writes, DECODE reads)
-  uint32_t tok_cap;     // COUNT: token budget
+  uint32_t tok_cap;     // COUNT: token budget; DECODE (replay): 0 = the job starts the stream, 32768 = unknown history before it
   uint32_t ntok;        // DECODE: tokens to replay, or kNoTokens = decode again
 };
 
@@ -112,6 +122,8 @@ DEFL_DEV void inflate_chunk_warp(WarpSmem& sm, const WarpScratch& sc, int lane, 
                                  const uint32_t* saved = nullptr, uint32_t nsaved = kNoTokens,
                                  uint32_t mode = MODE_BLOCK_STARTS, uint32_t start_final = FIN_UNKNOWN) {
   out.link_final = FIN_NO; out.has_eob = 0; out.eob_bytes = 0; out.eob_ntok = kNoTokens; out.eob_bit = 0;
+  out.npiece = 0;
+  uint32_t mark_pos = 0;                      // output position of the last piece mark
   if (!COUNT && saved && nsaved != kNoTokens) {
     // the COUNT pass kept this chunk's tokens: only the byte-producing half of the work is left
     uint32_t p = 0;
@@ -153,9 +165,29 @@ DEFL_DEV void inflate_chunk_warp(WarpSmem& sm, const WarpScratch& sc, int lane, 
       br.skip(3); br.norm();
     }
     if (btype == 0) {
-      if (sink) sink->ok = false;          // stored bytes are not tokens: such a chunk decodes again
+      const uint32_t pos0 = pos;
+      const uint64_t bit0 = br.bitpos();
       reason = stored_block_sym<SYM, COUNT>(lane, br, src, srclen, base_bit, dst, pos, cap);
       if (reason) break;
+      // kept tokens (COUNT pass): stored bytes go in as literal tokens, two to a token, so that such a chunk is only
+      // replayed in the DECODE pass like any other.  (An empty stored block -- what a flush leaves, 63 of them in a
+      // pigz-style stream -- adds nothing; before, every chunk holding one was decoded a second time, a whole chunk
+      // on one warp, and those 63 set the time of the pass.)
+      if (COUNT && sink && sink->buf && sink->ok && pos != pos0) {
+        const uint32_t len = pos - pos0, nt = (len + 1u) >> 1;
+        if (nt > sink->cap - sink->n) {
+          sink->ok = false;
+        } else {
+          const uint8_t* p = src + ((((bit0 - base_bit) + 7u) >> 3) + 4u);
+          for (uint32_t i = (uint32_t)lane; i < nt; i += 32u) {
+            const uint32_t b0 = simt::ld_in8(p + 2u * i);
+            const bool     two = 2u * i + 1u < len;
+            const uint32_t b1 = two ? simt::ld_in8(p + 2u * i + 1u) : 0u;
+            sink->buf[sink->n + i] = ((two ? 2u : 1u) << 24) | (b1 << 8) | b0;
+          }
+          sink->n += nt;
+        }
+      }
     } else if (btype == 3) {
       reason = R_BLOCK_TYPE;
       break;
@@ -180,6 +212,11 @@ DEFL_DEV void inflate_chunk_warp(WarpSmem& sm, const WarpScratch& sc, int lane, 
         }
         st = decode_window<SYM, COUNT>(sm, sc, lane, br.w, br.wend, end_bit, cur, dst, cap, pos, hist, sink, soft,
                                        btype == 1u ? kWarmFixed : kWarmDynamic);
+        if (COUNT && sink && sink->buf && sink->ok && out.npiece < kMaxPieces && pos - mark_pos >= kPieceBytes &&
+            (st == LS_OK || st == LS_EOB)) {
+          out.piece_tok[out.npiece] = sink->n; out.piece_pos[out.npiece] = pos; out.npiece++;
+          mark_pos = pos;
+        }
       } while (st == LS_OK);
       if (linked) {
         br.seek(cur);
@@ -261,6 +298,7 @@ split_chunk_kernel(const SplitStreamDesc* __restrict__ streams, const uint64_t* 
     k = simt::shfl(kFull, k, 0);
     if (k >= njobs) break;
     const SplitJob job = jobs[k];
+    if (!COUNT && tokbuf == nullptr && job.ntok != kNoTokens) continue;     // replayed by split_replay_kernel
     const SplitStreamDesc& sd = streams[job.stream];
     SplitChunkOut  o;
     TokSink        sink;
@@ -273,6 +311,43 @@ split_chunk_kernel(const SplitStreamDesc* __restrict__ streams, const uint64_t* 
                                         (!COUNT && tokbuf) ? tokbuf + job.tok_off : nullptr, job.ntok,
                                         sd.mode, job.start_final);
     if (lane == 0) outs[k] = o;
+    simt::syncwarp(kFull);
+  }
+}
+
+// C for the chunks whose tokens the COUNT pass kept (nearly all): only the resolver, in a kernel of its own.  A warp's
+// replay is a chain of dependent memory round trips (tokens -> sources -> stores), so what it needs is company: without
+// the decode tables (1 KiB of stage per warp instead of 5) and the decoder's registers, 12 CTAs x 4 warps fit an SM --
+// 7104 warps, so the ~4700 chunks of a 1 GiB stream run in ONE wave where split_chunk_kernel<false> (4144 warps) needed two.
+#ifndef DEFL_REPLAY_CTAS_PER_SM
+#define DEFL_REPLAY_CTAS_PER_SM 12
+#endif
+template <int WARPS>
+__global__ void __launch_bounds__(WARPS * 32, DEFL_REPLAY_CTAS_PER_SM)
+split_replay_kernel(const SplitJob* __restrict__ jobs, uint32_t njobs, uint16_t* __restrict__ sym,
+                    SplitChunkOut* __restrict__ outs, unsigned int* __restrict__ ticket,
+                    const uint32_t* __restrict__ tokbuf) {
+  __shared__ __align__(16) uint16_t stage[WARPS][kStageV3];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  for (;;) {
+    uint32_t k = 0;
+    if (lane == 0) k = atomicAdd(ticket, 1u);
+    k = simt::shfl(kFull, k, 0);
+    if (k >= njobs) break;
+    const SplitJob job = jobs[k];
+    if (job.ntok == kNoTokens) continue;                 // decoded again by split_chunk_kernel<false>
+    uint32_t p = 0;
+    simt::syncwarp(kFull);
+    const uint32_t r = resolve_tokens<uint16_t>(stage[warp], lane, tokbuf + job.tok_off, job.ntok, sym + job.out_off,
+                                                job.cap, p, job.tok_cap);      // DECODE jobs: tok_cap = symbols of unknown history
+    if (lane == 0) {
+      SplitChunkOut o;
+      o.npiece = 0;
+      o.link_final = FIN_NO; o.has_eob = 0; o.eob_bytes = 0; o.eob_ntok = kNoTokens; o.eob_bit = 0;
+      o.end_bit = 0; o.link = 0; o.ntok = job.ntok; o.out_bytes = p;
+      o.status = r ? (CH_FAIL | (r << 8)) : (uint32_t)CH_REPLAYED;
+      outs[k] = o;
+    }
     simt::syncwarp(kFull);
   }
 }

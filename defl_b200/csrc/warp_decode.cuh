@@ -377,7 +377,7 @@ template <> struct SymWord<uint16_t> { static constexpr uint32_t kPer = 2, kShif
 #define DEFL_LANE_WORDS 3   // 12 bytes: 189 GB/s on config 2 against 185 (16 bytes) and 154 (8 bytes), profiles/README.md round 2
 #endif
 #ifndef DEFL_LANE_WORDS16
-#define DEFL_LANE_WORDS16 4
+#define DEFL_LANE_WORDS16 6   // 12 symbols: mixed batch 80.5 -> 83.6 GB/s against 4 (72 registers; at 64 it spilled and lost)
 #endif
 // a lane copies matches of up to this many words' worth of symbols itself (bytes / 16-bit symbols)
 template <typename SYM> struct LaneWords { static constexpr uint32_t k = sizeof(SYM) == 2 ? DEFL_LANE_WORDS16 : DEFL_LANE_WORDS; };

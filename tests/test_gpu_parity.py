@@ -668,3 +668,54 @@ def test_degenerate_codes_and_window_shapes(gpu_lib):
     datas += more_d; caps += more_c
     res, outs = d.infl_buf_batch(datas, caps, 0)
     _check_against_port(d, res, outs, datas, caps, 0, "degenerate")
+
+
+@pytest.mark.gpu
+def test_split_replay_pieces_on_and_off(gpu_lib):
+    """The C pass replays a chunk's kept tokens whole or in pieces cut at decode-window ends (DEFL_SPLIT_PIECES = 0 / 1;
+    2 = by the fill rule): the same bytes, Adler-32 and positions either way, with stored blocks inside the streams
+    (their bytes are kept as literal tokens), on streams with and without flush points and at odd output alignments."""
+    import os
+    import torch
+    from defl_b200 import synth, api
+    d = gpu_lib
+    rng = np.random.default_rng(5)
+    raws = []
+    for seed, n in ((21, 9 << 20), (22, 14 << 20), (23, 6 << 20)):
+        raws.append(synth.make_streams([("text", n, seed, 6, zlib.Z_DEFAULT_STRATEGY)], threads=2)[0][0])
+    streams = []
+    # (a) one deflate history; (b) full flushes every ~1 MiB (empty stored blocks); (c) incompressible stretches inside
+    # compressible text: real stored blocks between dynamic ones
+    streams.append((raws[0], zlib.compress(raws[0], 6)))
+    c = zlib.compressobj(6)
+    z = b"".join(c.compress(raws[1][i:i + (1 << 20)]) + c.flush(zlib.Z_FULL_FLUSH) for i in range(0, len(raws[1]), 1 << 20)) + c.flush()
+    streams.append((raws[1], z))
+    mix = bytearray(raws[2])
+    for at in range(1 << 20, len(mix) - (300 << 10), 1 << 20):
+        mix[at:at + (200 << 10)] = rng.integers(0, 256, 200 << 10, dtype=np.uint8).tobytes()
+    mix = bytes(mix)
+    streams.append((mix, zlib.compress(mix, 6)))
+    dev = torch.device("cuda", 0)
+    srcs = [torch.frombuffer(bytearray(z), dtype=torch.uint8).to(dev) for _, z in streams]
+    flags = d.INFL_ZLIB | d.INFL_BATCH_VERIFY_ADLER | d.INFL_BATCH_DEVICE_PTRS
+    old = os.environ.get("DEFL_SPLIT_PIECES")
+    try:
+        for mode in ("0", "1", "2"):
+            os.environ["DEFL_SPLIT_PIECES"] = mode
+            dsts = [torch.zeros(len(r) + 8, dtype=torch.uint8, device=dev) for r, _ in streams]
+            items = np.zeros(len(streams), dtype=d.ITEM_DTYPE)
+            for i, ((raw, z), s, t) in enumerate(zip(streams, srcs, dsts)):
+                items[i] = (s.data_ptr(), len(z), t.data_ptr() + (i % 3), len(raw))
+            results = np.zeros(len(streams), dtype=d.RESULT_DTYPE)
+            api.infl_buf_batch_raw(items, flags, results)
+            torch.cuda.synchronize()
+            for i, ((raw, z), t, g) in enumerate(zip(streams, dsts, results)):
+                assert int(g["code"]) == 0 and int(g["info"]) & 4, (mode, i, int(g["code"]), hex(int(g["info"])))
+                assert int(g["outlen"]) == len(raw) and int(g["inpos"]) == len(z) - 4, (mode, i)   # the trailer is not deflate data
+                assert int(g["adler"]) == (zlib.adler32(raw) & 0xFFFFFFFF) == int(g["adler_stored"]), (mode, i)
+                assert t[(i % 3): (i % 3) + len(raw)].cpu().numpy().tobytes() == raw, (mode, i)
+    finally:
+        if old is None:
+            os.environ.pop("DEFL_SPLIT_PIECES", None)
+        else:
+            os.environ["DEFL_SPLIT_PIECES"] = old
