@@ -812,7 +812,7 @@ bool wants_split(const infl_batch_item_t& it, uint64_t batch_bytes, uint64_t res
   if (it.srclen >= kSplitMinBytes) return true;
   if (it.srclen < kSplitMinInBatch) return false;
   // DEFL_SPLIT_TAIL_PCT: a stream is split when its share of the batch exceeds this percentage of 1 / resident warps
-  static const uint32_t pct = env_u32("DEFL_SPLIT_TAIL_PCT", 60u, 1u, 100000u);
+  static const uint32_t pct = env_u32("DEFL_SPLIT_TAIL_PCT", 55u, 1u, 100000u);
   return (it.srclen + it.dstlen) * resident_warps * 100u > batch_bytes * pct;
 }
 
