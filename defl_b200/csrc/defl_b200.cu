@@ -950,32 +950,49 @@ int run_host_batch_on_device(const infl_batch_item_t* items, size_t n, int flags
       return fail("stream larger than 4 GiB - 1 (the reference API limit)");
     total += items[i].srclen + items[i].dstlen;
   }
-  // large streams first, one at a time, through the split-point decoder (they fill the GPU on their own)
+  // large streams first through the split-point decoder (each fills the GPU on its own), three slots deep: while
+  // member k decodes, member k + 1 is already on its way in and member k - 1 on its way home (each slot has its own
+  // stream and buffers; a slot is reused once the stream of its last user has drained)
   if (!(flags & INFL_BATCH_NO_SPLIT)) {
     bool any = false;
     for (size_t i = 0; i < n; i++) any = any || items[i].srclen >= kSplitMinBytes;
     if (any) {
       std::vector<infl_batch_item_t> rest;
-      std::vector<size_t>            rest_idx;
-      PipeSlot& S = HP.slot[0];
-      for (size_t i = 0; i < n; i++) {
-        int rc = UNZ_NOOP;
-        if (items[i].srclen >= kSplitMinBytes) {
-          if (S.d_in.reserve(items[i].srclen + 64) || S.d_out.reserve(items[i].dstlen + 64) ||
-              S.d_ws.reserve_exact(warp_kernel_workspace(E->sms)))
-            return UNZ_ERR;
-          // same alignment of the device copy as the host pointer's
-          uint8_t* din = static_cast<uint8_t*>(S.d_in.p) + ((uintptr_t)items[i].src & (kAlign - 1));
-          CU_TRY(cudaMemcpyAsync(din, items[i].src, items[i].srclen, cudaMemcpyHostToDevice, S.st), "H2D input");
-          rc = split_decode_device(E, din, items[i].srclen, static_cast<uint8_t*>(S.d_out.p), items[i].dstlen, flags,
-                                   S.d_ws.p, S.st, &results[i]);
-          if (rc == UNZ_ERR) return UNZ_ERR;
-          if (rc == UNZ_OK && results[i].outlen) {
-            CU_TRY(cudaMemcpyAsync(items[i].dst, S.d_out.p, results[i].outlen, cudaMemcpyDeviceToHost, S.st), "D2H output");
-            CU_TRY(cudaStreamSynchronize(S.st), "D2H output");
-          }
-        }
-        if (rc == UNZ_NOOP) { rest.push_back(items[i]); rest_idx.push_back(i); }
+      std::vector<size_t>            rest_idx, big;
+      for (size_t i = 0; i < n; i++) if (items[i].srclen >= kSplitMinBytes) big.push_back(i);
+      constexpr size_t kBigSlots = 3;
+      static_assert(kBigSlots <= (size_t)kPipeSlots, "slots of the host pipeline");
+      std::vector<uint8_t*> din(big.size(), nullptr);
+      auto upload = [&](size_t k) -> int {                          // H2D of large member k into its slot
+        PipeSlot& S = HP.slot[k % kBigSlots];
+        const size_t i = big[k];
+        CU_TRY(cudaStreamSynchronize(S.st), "large member: slot drain");          // member k - 3 is home
+        if (S.d_in.reserve(items[i].srclen + 64) || S.d_out.reserve(items[i].dstlen + 64) ||
+            S.d_ws.reserve_exact(warp_kernel_workspace(E->sms)))
+          return UNZ_ERR;
+        // same alignment of the device copy as the host pointer's
+        din[k] = static_cast<uint8_t*>(S.d_in.p) + ((uintptr_t)items[i].src & (kAlign - 1));
+        CU_TRY(cudaMemcpyAsync(din[k], items[i].src, items[i].srclen, cudaMemcpyHostToDevice, S.st), "H2D input");
+        return UNZ_OK;
+      };
+      std::vector<int> big_rc(big.size(), UNZ_NOOP);
+      if (!big.empty() && upload(0) != UNZ_OK) return UNZ_ERR;
+      for (size_t k = 0; k < big.size(); k++) {
+        if (k + 1 < big.size() && upload(k + 1) != UNZ_OK) return UNZ_ERR;
+        PipeSlot& S = HP.slot[k % kBigSlots];
+        const size_t i = big[k];
+        const int rc = split_decode_device(E, din[k], items[i].srclen, static_cast<uint8_t*>(S.d_out.p), items[i].dstlen, flags,
+                                           S.d_ws.p, S.st, &results[i]);
+        if (rc == UNZ_ERR) return UNZ_ERR;
+        big_rc[k] = rc;
+        if (rc == UNZ_OK && results[i].outlen)
+          CU_TRY(cudaMemcpyAsync(items[i].dst, S.d_out.p, results[i].outlen, cudaMemcpyDeviceToHost, S.st), "D2H output");
+      }
+      for (size_t s2 = 0; s2 < kBigSlots; s2++) CU_TRY(cudaStreamSynchronize(HP.slot[s2].st), "D2H output");
+      for (size_t i = 0, k = 0; i < n; i++) {
+        const bool is_big = k < big.size() && big[k] == i;
+        if (!is_big || big_rc[k] == UNZ_NOOP) { rest.push_back(items[i]); rest_idx.push_back(i); }
+        if (is_big) k++;
       }
       if (rest.empty()) return UNZ_OK;
       std::vector<infl_batch_result_t> rr(rest.size());

@@ -719,3 +719,27 @@ def test_split_replay_pieces_on_and_off(gpu_lib):
             os.environ.pop("DEFL_SPLIT_PIECES", None)
         else:
             os.environ["DEFL_SPLIT_PIECES"] = old
+
+
+@pytest.mark.gpu
+def test_large_host_members_pipelined(gpu_lib):
+    """Host-pointer batches whose members are >= 4 MiB compressed go through the split decoder one after another,
+    three slots deep (copy in / decode / copy home overlap): five such members between small ones, one of them damaged,
+    outputs at their own host buffers -- every record and byte as the oracle has it."""
+    from defl_b200 import synth
+    d = gpu_lib
+    specs = [("text", 15 << 20, 31, 6, zlib.Z_DEFAULT_STRATEGY), ("text", 70000, 32, 6, zlib.Z_DEFAULT_STRATEGY),
+             ("text", 17 << 20, 33, 6, zlib.Z_DEFAULT_STRATEGY), ("png", 9 << 20, 34, 6, zlib.Z_DEFAULT_STRATEGY),
+             ("log", 3000, 35, 9, zlib.Z_DEFAULT_STRATEGY), ("text", 16 << 20, 36, 1, zlib.Z_DEFAULT_STRATEGY),
+             ("text", 15 << 20, 37, 6, zlib.Z_DEFAULT_STRATEGY)]
+    streams = synth.make_streams(specs, threads=4)
+    datas = [z for _, z in streams]
+    big = [i for i, z in enumerate(datas) if len(z) >= (4 << 20)]
+    assert len(big) >= 4, [len(z) for z in datas]
+    bad = bytearray(datas[big[1]]); bad[len(bad) // 3] ^= 0x10
+    datas[big[1]] = bytes(bad)
+    caps = [len(r) for r, _ in streams]
+    for _ in range(2):                                   # the second call reuses the slots
+        res, outs = d.infl_buf_batch(datas, caps, d.INFL_ZLIB)
+        _check_against_port(d, res, outs, datas, caps, 1, "large host members")
+        assert sum(bool(int(g["info"]) & 4) for g in res) >= len(big) - 1
