@@ -933,6 +933,8 @@ int chunk_finish(PipeSlot& S, const infl_batch_item_t* items, infl_batch_result_
   return UNZ_OK;
 }
 
+int run_device_batch_locked(Engine* E, const infl_batch_item_t* items, size_t n, int flags, infl_batch_result_t* results);
+
 int run_host_batch_on_device(const infl_batch_item_t* items, size_t n, int flags,
                              infl_batch_result_t* results) {
   Engine* E = nullptr;
@@ -950,50 +952,74 @@ int run_host_batch_on_device(const infl_batch_item_t* items, size_t n, int flags
       return fail("stream larger than 4 GiB - 1 (the reference API limit)");
     total += items[i].srclen + items[i].dstlen;
   }
-  // large streams first through the split-point decoder (each fills the GPU on its own), three slots deep: while
-  // member k decodes, member k + 1 is already on its way in and member k - 1 on its way home (each slot has its own
-  // stream and buffers; a slot is reused once the stream of its last user has drained)
+  // large streams first: groups of them (about 512 MiB of output each) go through the device batch path TOGETHER -- one
+  // split decode for the whole group, which fills the GPU and pays the decoder's host round trips once -- three slots
+  // deep: while group g decodes, group g + 1 is already on its way in and group g - 1 on its way home (each slot has its
+  // own stream and buffers; a slot is reused once the stream of its last user has drained)
   if (!(flags & INFL_BATCH_NO_SPLIT)) {
     bool any = false;
     for (size_t i = 0; i < n; i++) any = any || items[i].srclen >= kSplitMinBytes;
     if (any) {
       std::vector<infl_batch_item_t> rest;
       std::vector<size_t>            rest_idx, big;
-      for (size_t i = 0; i < n; i++) if (items[i].srclen >= kSplitMinBytes) big.push_back(i);
+      for (size_t i = 0; i < n; i++) {
+        if (items[i].srclen >= kSplitMinBytes) big.push_back(i);
+        else { rest.push_back(items[i]); rest_idx.push_back(i); }
+      }
       constexpr size_t kBigSlots = 3;
       static_assert(kBigSlots <= (size_t)kPipeSlots, "slots of the host pipeline");
-      std::vector<uint8_t*> din(big.size(), nullptr);
-      auto upload = [&](size_t k) -> int {                          // H2D of large member k into its slot
-        PipeSlot& S = HP.slot[k % kBigSlots];
-        const size_t i = big[k];
-        CU_TRY(cudaStreamSynchronize(S.st), "large member: slot drain");          // member k - 3 is home
-        if (S.d_in.reserve(items[i].srclen + 64) || S.d_out.reserve(items[i].dstlen + 64) ||
-            S.d_ws.reserve_exact(warp_kernel_workspace(E->sms)))
-          return UNZ_ERR;
-        // same alignment of the device copy as the host pointer's
-        din[k] = static_cast<uint8_t*>(S.d_in.p) + ((uintptr_t)items[i].src & (kAlign - 1));
-        CU_TRY(cudaMemcpyAsync(din[k], items[i].src, items[i].srclen, cudaMemcpyHostToDevice, S.st), "H2D input");
+      constexpr size_t kGroupOut = (size_t)512 << 20;
+      std::vector<size_t> gfirst;                                    // group g = big[gfirst[g] .. gfirst[g + 1])
+      for (size_t k = 0, out = 0; k < big.size(); k++) {
+        if (k == 0 || out + items[big[k]].dstlen > kGroupOut) { gfirst.push_back(k); out = 0; }
+        out += items[big[k]].dstlen;
+      }
+      gfirst.push_back(big.size());
+      const size_t ngroups = gfirst.size() - 1;
+      std::vector<std::vector<infl_batch_item_t>> dev(ngroups);
+      static cudaEvent_t in_done[kMaxDevices][kBigSlots] = {};
+      auto upload = [&](size_t g) -> int {                          // H2D of group g into its slot
+        PipeSlot& S = HP.slot[g % kBigSlots];
+        CU_TRY(cudaStreamSynchronize(S.st), "large members: slot drain");         // group g - 3 is home
+        size_t in_bytes = 0, out_bytes = 0;
+        for (size_t k = gfirst[g]; k < gfirst[g + 1]; k++) {
+          in_bytes  = align_up(in_bytes) + kAlign + items[big[k]].srclen;
+          out_bytes = align_up(out_bytes) + items[big[k]].dstlen;
+        }
+        if (S.d_in.reserve(in_bytes + 64) || S.d_out.reserve(align_up(out_bytes) + 64)) return UNZ_ERR;
+        size_t ia = 0, oa = 0;
+        for (size_t k = gfirst[g]; k < gfirst[g + 1]; k++) {
+          const infl_batch_item_t& it = items[big[k]];
+          // same alignment of the device copy as the host pointer's
+          ia = align_up(ia);
+          uint8_t* din = static_cast<uint8_t*>(S.d_in.p) + ia + ((uintptr_t)it.src & (kAlign - 1));
+          oa = align_up(oa);
+          CU_TRY(cudaMemcpyAsync(din, it.src, it.srclen, cudaMemcpyHostToDevice, S.st), "H2D input");
+          infl_batch_item_t dv;
+          dv.src = din; dv.srclen = it.srclen; dv.dst = static_cast<uint8_t*>(S.d_out.p) + oa; dv.dstlen = it.dstlen;
+          dev[g].push_back(dv);
+          ia += kAlign + it.srclen;
+          oa += it.dstlen;
+        }
+        cudaEvent_t& ev = in_done[E->dev][g % kBigSlots];
+        if (!ev) CU_TRY(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming), "cudaEventCreate");
+        CU_TRY(cudaEventRecord(ev, S.st), "cudaEventRecord");
         return UNZ_OK;
       };
-      std::vector<int> big_rc(big.size(), UNZ_NOOP);
-      if (!big.empty() && upload(0) != UNZ_OK) return UNZ_ERR;
-      for (size_t k = 0; k < big.size(); k++) {
-        if (k + 1 < big.size() && upload(k + 1) != UNZ_OK) return UNZ_ERR;
-        PipeSlot& S = HP.slot[k % kBigSlots];
-        const size_t i = big[k];
-        const int rc = split_decode_device(E, din[k], items[i].srclen, static_cast<uint8_t*>(S.d_out.p), items[i].dstlen, flags,
-                                           S.d_ws.p, S.st, &results[i]);
-        if (rc == UNZ_ERR) return UNZ_ERR;
-        big_rc[k] = rc;
-        if (rc == UNZ_OK && results[i].outlen)
-          CU_TRY(cudaMemcpyAsync(items[i].dst, S.d_out.p, results[i].outlen, cudaMemcpyDeviceToHost, S.st), "D2H output");
+      if (ngroups && upload(0) != UNZ_OK) return UNZ_ERR;
+      for (size_t g = 0; g < ngroups; g++) {
+        if (g + 1 < ngroups && upload(g + 1) != UNZ_OK) return UNZ_ERR;
+        PipeSlot& S = HP.slot[g % kBigSlots];
+        CU_TRY(cudaStreamWaitEvent(E->stream, in_done[E->dev][g % kBigSlots], 0), "cudaStreamWaitEvent");
+        std::vector<infl_batch_result_t> gr(dev[g].size());
+        if (run_device_batch_locked(E, dev[g].data(), dev[g].size(), flags, gr.data()) != UNZ_OK) return UNZ_ERR;
+        for (size_t k = gfirst[g], j = 0; k < gfirst[g + 1]; k++, j++) {
+          results[big[k]] = gr[j];
+          if (gr[j].outlen)                                          // what was produced goes home, failed or not
+            CU_TRY(cudaMemcpyAsync(items[big[k]].dst, dev[g][j].dst, gr[j].outlen, cudaMemcpyDeviceToHost, S.st), "D2H output");
+        }
       }
       for (size_t s2 = 0; s2 < kBigSlots; s2++) CU_TRY(cudaStreamSynchronize(HP.slot[s2].st), "D2H output");
-      for (size_t i = 0, k = 0; i < n; i++) {
-        const bool is_big = k < big.size() && big[k] == i;
-        if (!is_big || big_rc[k] == UNZ_NOOP) { rest.push_back(items[i]); rest_idx.push_back(i); }
-        if (is_big) k++;
-      }
       if (rest.empty()) return UNZ_OK;
       std::vector<infl_batch_result_t> rr(rest.size());
       guard.unlock();
