@@ -968,7 +968,7 @@ int run_host_batch_on_device(const infl_batch_item_t* items, size_t n, int flags
       }
       constexpr size_t kBigSlots = 3;
       static_assert(kBigSlots <= (size_t)kPipeSlots, "slots of the host pipeline");
-      constexpr size_t kGroupOut = (size_t)512 << 20;
+      const size_t kGroupOut = (size_t)env_u32("DEFL_BIG_GROUP_MIB", 512u, 16u, 1u << 20) << 20;     // experiments: profiles/README.md
       std::vector<size_t> gfirst;                                    // group g = big[gfirst[g] .. gfirst[g + 1])
       for (size_t k = 0, out = 0; k < big.size(); k++) {
         if (k == 0 || out + items[big[k]].dstlen > kGroupOut) { gfirst.push_back(k); out = 0; }

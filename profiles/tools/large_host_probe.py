@@ -16,8 +16,11 @@ for i in range(n):
     items[i] = (src[i].data_ptr(), len(zs[i]), dst[i].data_ptr(), len(raws[i]))
 res = np.zeros(n, dtype=d.RESULT_DTYPE)
 flags = d.INFL_ZLIB | d.INFL_BATCH_VERIFY_ADLER
-for it in range(3):
-    t = time.perf_counter(); api.infl_buf_batch_raw(items, flags, res); dt = time.perf_counter() - t
-    assert (res["code"] == 0).all()
-    print("members %d x %d MiB: %.1f ms, %.1f GB/s decoded host to host" % (n, mib, dt * 1e3, sum(map(len, raws)) / dt / 1e9))
+import os
+for grp in (os.environ.get("PROBE_GROUPS", "512").split(",")):
+    os.environ["DEFL_BIG_GROUP_MIB"] = grp
+    for it in range(3):
+        t = time.perf_counter(); api.infl_buf_batch_raw(items, flags, res); dt = time.perf_counter() - t
+        assert (res["code"] == 0).all()
+    print("group %s MiB, members %d x %d MiB: %.1f ms, %.1f GB/s decoded host to host" % (grp, n, mib, dt * 1e3, sum(map(len, raws)) / dt / 1e9))
 assert dst[n - 1].numpy().tobytes() == raws[n - 1]
