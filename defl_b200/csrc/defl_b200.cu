@@ -581,9 +581,11 @@ int split_decode_many(Engine* E, const SplitInput* in, size_t nin, int flags, vo
   struct ChainItem { uint32_t stream, cand; uint64_t off; uint32_t bytes, ntok, start_final; bool ends; uint32_t tok0; bool sub; };
   // Pieces pay when the chunks alone do not fill the replay kernel (one big stream: 4700 chunks of uneven length for
   // ~7100 warps, C pass 10.5 -> 5.2 ms per GiB); a batch of many split members has chunks enough, and there the extra
-  // windows only cost (mixed workload 83.5 -> 75.9 GB/s with pieces).  DEFL_SPLIT_PIECES: 0 never, 1 always, 2 by that rule.
+  // windows only cost (mixed workload 83.5 -> 75.9 GB/s with pieces; a 1 GiB single-history stream with 6738 candidates
+  // 61.2 -> 57.9: its D1 by doubling pays per window).  DEFL_SPLIT_PIECES: 0 never, 1 always, 2 = when the candidates
+  // fill less than 0.8 of the replay kernel's 48 warps per SM.
   const uint32_t pieces_mode = env_u32("DEFL_SPLIT_PIECES", 2, 0, 2);
-  const bool pieces = pieces_mode == 1u || (pieces_mode == 2u && (uint64_t)ncand * 2u <= (uint64_t)E->sms * 48u * 3u);
+  const bool pieces = pieces_mode == 1u || (pieces_mode == 2u && (uint64_t)ncand * 5u <= (uint64_t)E->sms * 48u * 4u);
   std::vector<ChainItem> chain;
   std::vector<uint64_t>  off;                                      // per stream nchunk + 1 entries
   std::vector<uint64_t>  end_bit(ns, 0);
